@@ -1,0 +1,716 @@
+// Host side of the GPU engine: buffers, plan, peer wiring, pass scheduling.
+//
+// Reference counterparts (behaviour, not code):
+//   GPU_convolution()      cuda/cuda_convolution.cu:49-102  (alloc, H2D, loop, D2H)
+//   padded double buffers  mpi/mpi_convolution.c:104-124
+//   halo post/wait/swap    mpi/mpi_convolution.c:156-240
+// B200 design: two framed, pitched ping-pong buffers per rank; neighbours write
+// straight into the frame over NVLink from inside the stencil kernel; the host
+// only enqueues one kernel per K fused iterations (optionally as a CUDA graph).
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "common.h"
+#include "kernels.h"
+#include "stencil_stream.cuh"
+#include "stencil_tma.h"
+
+#define CK(call)                                                                         \
+    do {                                                                                 \
+        cudaError_t e_ = (call);                                                         \
+        if (e_ != cudaSuccess) {                                                         \
+            b2c::set_error("%s:%d: %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); \
+            return B2C_ECUDA;                                                            \
+        }                                                                                \
+    } while (0)
+
+using namespace b2c;
+
+namespace {
+
+// Flag pad layout, in 32-bit words.  Every flag/counter sits on its own 128 B line.
+constexpr int kPadFlags = 0;          // 8 x 32
+constexpr int kPadCounters = 256;     // 8 x 32
+constexpr int kPadSlots = 512;        // up to 64 ranks
+constexpr int kPadChanged = 640;
+constexpr int kPadConverged = 641;
+constexpr int kPadConvergedAt = 642;
+constexpr int kPadWords = 1024;
+constexpr int kMaxRanks = 64;
+
+struct Blob {  // what b2c_engine_export ships; must fit B2C_HANDLE_BYTES
+    cudaIpcMemHandle_t buf[2];
+    cudaIpcMemHandle_t pad;
+    int rank, device, pid;
+    long long alloc_bytes;
+};
+static_assert(sizeof(Blob) <= B2C_HANDLE_BYTES, "blob too large");
+
+struct Pass {
+    int k;
+    bool check;
+    unsigned iters_after;
+};
+
+struct BandPlan {
+    int hlo, vw, nbands, nchunks, chunk_rows, nbw, nbe;
+};
+
+}  // namespace
+
+struct b2c_engine {
+    int device = 0, W = 0, H = 0, CH = 1, P = 1, Q = 1, rank = 0;
+    int R = 0, C = 0, row0 = 0, col0 = 0, bw = 0;
+    b2c_opts opts{};
+    int nb[8];
+    bool any_nb = false;
+    long long pitch = 0, alloc_bytes = 0;
+    uint8_t *alloc[2] = {nullptr, nullptr};
+    uint8_t *base[2] = {nullptr, nullptr};
+    uint32_t *pad = nullptr;
+    // compat buffers (tight, +2 slack rows)
+    uint8_t *cbuf[2] = {nullptr, nullptr};
+    long long cbytes = 0;
+    // peers
+    bool connected = false;
+    uint8_t *peer_base[2][8];
+    uint32_t *peer_pad[8];
+    uint32_t *rank_pad[kMaxRanks];
+    std::vector<void *> ipc_opened;
+    // state
+    int cur = 0;
+    uint32_t epoch = 0;      // pushes completed so far (same on every rank)
+    unsigned check_seq = 0;
+    int iters_done = 0;
+    bool pending_converge_fixup = false;
+    std::vector<Pass> last_passes;
+    uint32_t run_epoch0 = 0;
+    int run_cur0 = 0;
+    // plan
+    int kernel = B2C_KERNEL_STREAM, K = 4, SB = 16, F = 1;
+    int sm_count = 148;
+    long long delay = 0;
+    long long launches = 0;
+    std::map<std::pair<int, int>, cudaGraphExec_t> graphs;
+    NaiveWeights nw{};
+    TmaState *tma = nullptr;
+};
+
+namespace {
+
+BandPlan make_band_plan(const b2c_engine *e, int k) {
+    BandPlan bp{};
+    const int SB = e->SB, CH = e->CH;
+    bp.hlo = (int)round_up((long long)k * CH, SB);
+    bp.vw = (int)round_down(32 * SB - bp.hlo - k * CH, SB);
+    bp.nbands = (int)ceil_div(e->bw, bp.vw);
+    // rows per warp: enough warps for ~2 waves of 16 warps/SM, but keep the 2k-row
+    // pipeline fill below ~12% of a chunk.
+    const long long target = (long long)e->sm_count * 32;
+    int chunk_rows = e->opts.chunk_rows;
+    if (chunk_rows <= 0) {
+        long long want = std::max<long long>(1, target / bp.nbands);
+        chunk_rows = (int)ceil_div(e->R, want);
+        chunk_rows = std::max(chunk_rows, std::max(16 * k, 32));
+    }
+    chunk_rows = std::max(chunk_rows, e->F);
+    chunk_rows = std::min(chunk_rows, std::max(e->R, 1));
+    chunk_rows = std::max(chunk_rows, 1);
+    bp.chunk_rows = chunk_rows;
+    bp.nchunks = (int)ceil_div(e->R, chunk_rows);
+    // re-balance so the last chunk is not a sliver
+    bp.chunk_rows = (int)ceil_div(e->R, bp.nchunks);
+    if (bp.chunk_rows < e->F) bp.chunk_rows = std::min(e->F, e->R);
+    bp.nchunks = (int)ceil_div(e->R, bp.chunk_rows);
+    const int fb = e->F * CH;
+    bp.nbw = std::min(bp.nbands, (int)ceil_div(fb, bp.vw));
+    bp.nbe = bp.nbands - (int)(std::max(0, e->bw - fb) / bp.vw);
+    bp.nbe = std::max(1, std::min(bp.nbands, bp.nbe));
+    return bp;
+}
+
+void fill_pass_params(const b2c_engine *e, int k, bool check, int src_i, PassParams &p) {
+    const BandPlan bp = make_band_plan(e, k);
+    memset(&p, 0, sizeof p);
+    p.src = e->base[src_i];
+    p.dst = e->base[src_i ^ 1];
+    p.pitch = e->pitch;
+    p.rows = e->R;
+    p.bw = e->bw;
+    p.nbands = bp.nbands;
+    p.nchunks = bp.nchunks;
+    p.chunk_rows = bp.chunk_rows;
+    p.vw = bp.vw;
+    p.hlo = bp.hlo;
+    const bool zero = e->opts.boundary == B2C_ZERO;
+    p.zero_n = zero && e->nb[B2C_N] < 0;
+    p.zero_s = zero && e->nb[B2C_S] < 0;
+    p.zero_w = zero && e->nb[B2C_W] < 0;
+    p.zero_e = zero && e->nb[B2C_E] < 0;
+    p.changed = check ? e->pad + kPadChanged : nullptr;
+    p.converged = e->opts.check_every > 0 ? e->pad + kPadConverged : nullptr;
+    HaloParams &h = p.halo;
+    h.nbw = bp.nbw;
+    h.nbe = bp.nbe;
+    h.enabled = e->any_nb ? 1 : 0;
+    if (!h.enabled) return;
+    h.push = (e->bw % e->SB == 0) ? 1 : 0;
+    h.depth = e->F;
+    h.wait_epoch = e->epoch;
+    h.post_epoch = e->epoch + 1;
+    h.flags = e->pad + kPadFlags;
+    h.counters = e->pad + kPadCounters;
+    h.delay = e->delay;
+    const int exp[8] = {bp.nbands, bp.nbands, bp.nbw * bp.nchunks, bp.nbe * bp.nchunks,
+                        bp.nbw, bp.nbe, bp.nbw, bp.nbe};
+    for (int d = 0; d < 8; ++d) {
+        h.expected[d] = exp[d];
+        if (e->nb[d] < 0) continue;
+        h.peer_dst[d] = e->peer_base[src_i ^ 1][d];
+        // the neighbour sees our data arriving from the opposite direction
+        h.peer_flag[d] = e->peer_pad[d] + kPadFlags + opposite_dir(d) * 32;
+    }
+}
+
+void fill_push_params(const b2c_engine *e, int buf_i, bool wait, PushParams &q) {
+    memset(&q, 0, sizeof q);
+    q.src = e->base[buf_i];
+    q.pitch = e->pitch;
+    q.rows = e->R;
+    q.bw = e->bw;
+    q.ch = e->CH;
+    q.depth = e->F;
+    q.flags = e->pad + kPadFlags;
+    q.counters = e->pad + kPadCounters;
+    q.post_epoch = e->epoch + 1;
+    q.wait_epoch = e->epoch;
+    q.wait_epoch_valid = wait ? 1 : 0;
+    for (int d = 0; d < 8; ++d) {
+        if (e->nb[d] < 0) continue;
+        q.peer_dst[d] = e->peer_base[buf_i][d];
+        q.peer_flag[d] = e->peer_pad[d] + kPadFlags + opposite_dir(d) * 32;
+    }
+}
+
+// Splits `reps` iterations into passes of k in {K, ..., 2, 1}; a pass ends on
+// every multiple of check_every (counted from the start of this run).
+std::vector<Pass> make_passes(const b2c_engine *e, int reps) {
+    std::vector<Pass> v;
+    const int ce = e->opts.check_every;
+    int done = 0;
+    while (done < reps) {
+        int limit = reps - done;
+        if (ce > 0) limit = std::min(limit, ce - done % ce);
+        int k = e->K;
+        while (k > limit) k >>= 1;
+        done += k;
+        v.push_back({k, ce > 0 && done % ce == 0, (unsigned)done});
+    }
+    return v;
+}
+
+int enqueue_pass(b2c_engine *e, const Pass &ps, cudaStream_t s) {
+    if (e->kernel == B2C_KERNEL_NAIVE) {
+        CK(launch_naive(e->base[e->cur], e->base[e->cur ^ 1], e->pitch, e->R, e->bw, e->CH, e->nw, s));
+        e->launches++;
+        if (e->any_nb) {
+            PushParams q;
+            fill_push_params(e, e->cur ^ 1, true, q);
+            CK(launch_halo_push(q, s));
+            e->launches++;
+        }
+    } else {
+        PassParams p;
+        fill_pass_params(e, ps.k, ps.check, e->cur, p);
+        if (e->kernel == B2C_KERNEL_TMA)
+            CK(launch_stream_tma(e->tma, p, e->cur, ps.k, e->SB, e->CH, ps.check, s));
+        else
+            CK(launch_stream(p, ps.k, e->SB, e->CH, ps.check, s));
+        e->launches++;
+        if (e->any_nb && !p.halo.push) {
+            PushParams q;
+            fill_push_params(e, e->cur ^ 1, false, q);
+            CK(launch_halo_push(q, s));
+            e->launches++;
+        }
+    }
+    e->cur ^= 1;
+    if (e->any_nb) e->epoch++;
+    if (ps.check) {
+        ConvergeParams c{};
+        c.changed = e->pad + kPadChanged;
+        c.slots = e->pad + kPadSlots;
+        const int n = e->P * e->Q;
+        for (int k = 0; k < n; ++k) c.peer_slots[k] = (n == 1 ? e->pad : e->rank_pad[k]) + kPadSlots;
+        c.nranks = n;
+        c.rank = e->rank;
+        c.seq = ++e->check_seq;
+        c.converged = e->pad + kPadConverged;
+        c.converged_at = e->pad + kPadConvergedAt;
+        c.iters_after = ps.iters_after;
+        CK(launch_converge(c, s));
+        e->launches++;
+    }
+    return B2C_OK;
+}
+
+void choose_plan(b2c_engine *e) {
+    const b2c_opts &o = e->opts;
+    e->kernel = o.kernel == B2C_KERNEL_AUTO ? B2C_KERNEL_STREAM : o.kernel;
+    if (o.filter != B2C_GAUSSIAN) e->kernel = B2C_KERNEL_NAIVE;
+    int K = o.tb > 0 ? o.tb : 4;
+    if (K >= 8) K = 8; else if (K >= 4) K = 4; else if (K >= 2) K = 2; else K = 1;
+    if (e->kernel == B2C_KERNEL_NAIVE) K = 1;
+    // a k-deep halo must come from the adjacent rank only
+    if (e->any_nb) while (K > 1 && K > std::min(e->R, e->C)) K >>= 1;
+    int SB = o.strip_bytes;
+    if (SB != 4 && SB != 8 && SB != 16) {
+        // widest strip that still yields enough warps to fill the machine
+        SB = 16;
+        while (SB > 4) {
+            const int nwords = SB / 4;
+            if (K * nwords <= 16) {
+                const int hlo = (int)round_up((long long)K * e->CH, SB);
+                const int vw = (int)round_down(32 * SB - hlo - K * e->CH, SB);
+                const long long warps = ceil_div(e->bw, vw) * ceil_div(e->R, std::max(16 * K, 32));
+                if (warps >= (long long)e->sm_count * 8) break;
+            }
+            SB >>= 1;
+        }
+    }
+    while (K * (SB / 4) > 16) SB >>= 1;
+    if (e->kernel == B2C_KERNEL_TMA) SB = 16;
+    e->K = K;
+    e->SB = SB;
+    e->F = e->any_nb ? K : 1;
+    if (e->kernel == B2C_KERNEL_NAIVE) e->F = 1;
+}
+
+int alloc_buffers(b2c_engine *e) {
+    CK(cudaSetDevice(e->device));
+    if (e->opts.boundary == B2C_CUDA_COMPAT) {
+        e->cbytes = (long long)e->W * e->CH * (e->H + 2);
+        for (auto &b : e->cbuf) {
+            CK(cudaMalloc(&b, (size_t)e->cbytes + 64));
+            CK(cudaMemset(b, 0, (size_t)e->cbytes + 64));
+        }
+    } else {
+        e->pitch = round_up(kLeftPad + (long long)e->bw + 32 + 16, 128);
+        e->alloc_bytes = e->pitch * (e->R + 2 * kFrameRows) + 1024;  // tail slack: last band's window
+        for (int i = 0; i < 2; ++i) {
+            CK(cudaMalloc(&e->alloc[i], (size_t)e->alloc_bytes));
+            CK(cudaMemset(e->alloc[i], 0, (size_t)e->alloc_bytes));
+            e->base[i] = e->alloc[i] + (long long)kFrameRows * e->pitch + kLeftPad;
+        }
+    }
+    CK(cudaMalloc(&e->pad, kPadWords * sizeof(uint32_t)));
+    CK(cudaMemset(e->pad, 0, kPadWords * sizeof(uint32_t)));
+    CK(cudaDeviceSynchronize());
+    return B2C_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+void b2c_default_opts(b2c_opts *o) {
+    memset(o, 0, sizeof *o);
+    o->boundary = B2C_ZERO;
+    o->filter = B2C_GAUSSIAN;
+    o->kernel = B2C_KERNEL_AUTO;
+    o->use_graph = -1;
+}
+
+b2c_engine *b2c_engine_create(int device, int W, int H, int CH, int P, int Q, int rank, const b2c_opts *opts) {
+    b2c_opts o;
+    if (opts) o = *opts; else b2c_default_opts(&o);
+    if (W <= 0 || H <= 0 || (CH != 1 && CH != 3) || P <= 0 || Q <= 0 || rank < 0 || rank >= P * Q ||
+        H % P || W % Q || P * Q > kMaxRanks) {
+        set_error("engine_create: bad geometry W=%d H=%d CH=%d grid=%dx%d rank=%d", W, H, CH, P, Q, rank);
+        return nullptr;
+    }
+    if (o.boundary == B2C_CUDA_COMPAT && (P * Q != 1 || o.filter != B2C_GAUSSIAN)) {
+        set_error("cuda-compat is single-GPU, gaussian only (like cuda/cuda_convolution.cu)");
+        return nullptr;
+    }
+    if ((long long)W / Q * CH > (1ll << 30)) {
+        set_error("block row too wide");
+        return nullptr;
+    }
+    b2c_engine *e = new b2c_engine();
+    e->device = device; e->W = W; e->H = H; e->CH = CH; e->P = P; e->Q = Q; e->rank = rank;
+    e->opts = o;
+    e->R = H / P; e->C = W / Q;
+    e->row0 = (rank / Q) * e->R;   // mpi_convolution.c:85-86
+    e->col0 = (rank % Q) * e->C;
+    e->bw = e->C * CH;
+    b2c_neighbours(rank, P, Q, o.boundary, e->nb);
+    e->any_nb = false;
+    for (int d = 0; d < 8; ++d) e->any_nb |= e->nb[d] >= 0;
+    memset(e->peer_base, 0, sizeof e->peer_base);
+    memset(e->peer_pad, 0, sizeof e->peer_pad);
+    memset(e->rank_pad, 0, sizeof e->rank_pad);
+    const FilterDef &f = filter_def(o.filter);
+    for (int i = 0; i < 3; ++i)
+        for (int j = 0; j < 3; ++j) {
+            e->nw.iw[i][j] = f.w[i][j];
+            e->nw.fw[i][j] = (float)(f.w[i][j] / (double)f.den);
+        }
+    e->nw.integer16 = f.den == 16;
+    int smc = 148;
+    if (cudaSetDevice(device) != cudaSuccess ||
+        cudaDeviceGetAttribute(&smc, cudaDevAttrMultiProcessorCount, device) != cudaSuccess) {
+        set_error("cudaSetDevice(%d) failed: %s", device, cudaGetErrorString(cudaGetLastError()));
+        delete e;
+        return nullptr;
+    }
+    e->sm_count = smc;
+    choose_plan(e);
+    if (alloc_buffers(e) != B2C_OK) {
+        b2c_engine_destroy(e);
+        return nullptr;
+    }
+    if (e->kernel == B2C_KERNEL_TMA && o.boundary != B2C_CUDA_COMPAT) {
+        e->tma = tma_create(e->alloc, e->pitch, e->R + 2 * kFrameRows, e->alloc_bytes);
+        if (!e->tma) {
+            b2c_engine_destroy(e);
+            return nullptr;
+        }
+    }
+    // A torus rank that is its own neighbour in every direction needs no peers.
+    bool self_only = e->any_nb;
+    for (int d = 0; d < 8; ++d) self_only &= (e->nb[d] < 0 || e->nb[d] == rank);
+    if (self_only && e->any_nb) {
+        b2c_engine *self = e;
+        b2c_engine_connect_local(&self, 1);
+    }
+    return e;
+}
+
+void b2c_engine_destroy(b2c_engine *e) {
+    if (!e) return;
+    cudaSetDevice(e->device);
+    cudaDeviceSynchronize();
+    for (auto &g : e->graphs) cudaGraphExecDestroy(g.second);
+    for (void *p : e->ipc_opened) cudaIpcCloseMemHandle(p);
+    if (e->tma) tma_destroy(e->tma);
+    for (auto &b : e->alloc) if (b) cudaFree(b);
+    for (auto &b : e->cbuf) if (b) cudaFree(b);
+    if (e->pad) cudaFree(e->pad);
+    delete e;
+}
+
+int b2c_engine_block(const b2c_engine *e, int *row0, int *col0, int *rows, int *cols) {
+    if (!e) return B2C_EINVAL;
+    if (row0) *row0 = e->row0;
+    if (col0) *col0 = e->col0;
+    if (rows) *rows = e->R;
+    if (cols) *cols = e->C;
+    return B2C_OK;
+}
+
+int b2c_engine_export(b2c_engine *e, void *out) {
+    if (!e || !out || e->opts.boundary == B2C_CUDA_COMPAT) return B2C_EINVAL;
+    CK(cudaSetDevice(e->device));
+    Blob b;
+    memset(&b, 0, sizeof b);
+    CK(cudaIpcGetMemHandle(&b.buf[0], e->alloc[0]));
+    CK(cudaIpcGetMemHandle(&b.buf[1], e->alloc[1]));
+    CK(cudaIpcGetMemHandle(&b.pad, e->pad));
+    b.rank = e->rank;
+    b.device = e->device;
+    b.pid = 0;
+    b.alloc_bytes = e->alloc_bytes;
+    memset(out, 0, B2C_HANDLE_BYTES);
+    memcpy(out, &b, sizeof b);
+    return B2C_OK;
+}
+
+int b2c_engine_import(b2c_engine *e, const void *blobs, int n) {
+    if (!e || !blobs || n != e->P * e->Q) {
+        set_error("engine_import: need %d blobs", e ? e->P * e->Q : 0);
+        return B2C_EINVAL;
+    }
+    CK(cudaSetDevice(e->device));
+    std::vector<uint8_t *> rbuf0((size_t)n, nullptr), rbuf1((size_t)n, nullptr);
+    const long long org = (long long)kFrameRows * e->pitch + kLeftPad;
+    for (int k = 0; k < n; ++k) {
+        Blob b;
+        memcpy(&b, (const uint8_t *)blobs + (size_t)k * B2C_HANDLE_BYTES, sizeof b);
+        if (b.rank != k || b.alloc_bytes != e->alloc_bytes) {
+            set_error("engine_import: blob %d does not match (rank %d, bytes %lld)", k, b.rank, b.alloc_bytes);
+            return B2C_EINVAL;
+        }
+        if (k == e->rank) {
+            e->rank_pad[k] = e->pad;
+            rbuf0[k] = e->alloc[0];
+            rbuf1[k] = e->alloc[1];
+            continue;
+        }
+        void *p = nullptr;
+        CK(cudaIpcOpenMemHandle(&p, b.pad, cudaIpcMemLazyEnablePeerAccess));
+        e->ipc_opened.push_back(p);
+        e->rank_pad[k] = (uint32_t *)p;
+        bool is_nb = false;
+        for (int d = 0; d < 8; ++d) is_nb |= e->nb[d] == k;
+        if (!is_nb) continue;
+        CK(cudaIpcOpenMemHandle(&p, b.buf[0], cudaIpcMemLazyEnablePeerAccess));
+        e->ipc_opened.push_back(p);
+        rbuf0[k] = (uint8_t *)p;
+        CK(cudaIpcOpenMemHandle(&p, b.buf[1], cudaIpcMemLazyEnablePeerAccess));
+        e->ipc_opened.push_back(p);
+        rbuf1[k] = (uint8_t *)p;
+    }
+    for (int d = 0; d < 8; ++d) {
+        const int k = e->nb[d];
+        if (k < 0) continue;
+        e->peer_base[0][d] = rbuf0[k] + org;
+        e->peer_base[1][d] = rbuf1[k] + org;
+        e->peer_pad[d] = e->rank_pad[k];
+    }
+    e->connected = true;
+    return B2C_OK;
+}
+
+int b2c_engine_connect_local(b2c_engine **engines, int n) {
+    if (!engines || n <= 0 || n != engines[0]->P * engines[0]->Q) {
+        set_error("connect_local: need one engine per rank");
+        return B2C_EINVAL;
+    }
+    for (int k = 0; k < n; ++k)
+        if (engines[k]->rank != k || engines[k]->pitch != engines[0]->pitch) {
+            set_error("connect_local: engines must be in rank order with identical geometry");
+            return B2C_EINVAL;
+        }
+    for (int a = 0; a < n; ++a)
+        for (int b = 0; b < n; ++b) {
+            if (engines[a]->device == engines[b]->device) continue;
+            CK(cudaSetDevice(engines[a]->device));
+            cudaError_t er = cudaDeviceEnablePeerAccess(engines[b]->device, 0);
+            if (er != cudaSuccess && er != cudaErrorPeerAccessAlreadyEnabled) CK(er);
+            cudaGetLastError();
+        }
+    for (int a = 0; a < n; ++a) {
+        b2c_engine *e = engines[a];
+        for (int k = 0; k < n; ++k) e->rank_pad[k] = engines[k]->pad;
+        for (int d = 0; d < 8; ++d) {
+            const int k = e->nb[d];
+            if (k < 0) continue;
+            e->peer_base[0][d] = engines[k]->base[0];
+            e->peer_base[1][d] = engines[k]->base[1];
+            e->peer_pad[d] = engines[k]->pad;
+        }
+        e->connected = true;
+    }
+    return B2C_OK;
+}
+
+static int copy_block(b2c_engine *e, void *user, long long upitch, cudaMemcpyKind kind, bool to_engine, void *stream) {
+    if (!e || !user) return B2C_EINVAL;
+    CK(cudaSetDevice(e->device));
+    cudaStream_t s = (cudaStream_t)stream;
+    if (e->opts.boundary == B2C_CUDA_COMPAT) {
+        const long long row = (long long)e->W * e->CH;
+        if (upitch <= 0) upitch = row;
+        if (to_engine) {
+            CK(cudaMemsetAsync(e->cbuf[0], 0, (size_t)e->cbytes, s));
+            CK(cudaMemsetAsync(e->cbuf[1], 0, (size_t)e->cbytes, s));  // cudaMemset(d_dst, 0), :61
+            CK(cudaMemcpy2DAsync(e->cbuf[0], (size_t)row, user, (size_t)upitch, (size_t)row, (size_t)e->H, kind, s));
+        } else {
+            CK(cudaMemcpy2DAsync(user, (size_t)upitch, e->cbuf[0], (size_t)row, (size_t)row, (size_t)e->H, kind, s));
+        }
+        return B2C_OK;
+    }
+    if (upitch <= 0) upitch = e->bw;
+    if (to_engine)
+        CK(cudaMemcpy2DAsync(e->base[e->cur], (size_t)e->pitch, user, (size_t)upitch, (size_t)e->bw, (size_t)e->R, kind, s));
+    else
+        CK(cudaMemcpy2DAsync(user, (size_t)upitch, e->base[e->cur], (size_t)e->pitch, (size_t)e->bw, (size_t)e->R, kind, s));
+    return B2C_OK;
+}
+
+int b2c_engine_upload(b2c_engine *e, const uint8_t *host, int64_t pitch, void *stream) {
+    return copy_block(e, (void *)host, pitch, cudaMemcpyHostToDevice, true, stream);
+}
+int b2c_engine_download(b2c_engine *e, uint8_t *host, int64_t pitch, void *stream) {
+    return copy_block(e, host, pitch, cudaMemcpyDeviceToHost, false, stream);
+}
+int b2c_engine_load_device(b2c_engine *e, const uint8_t *dev, int64_t pitch, void *stream) {
+    return copy_block(e, (void *)dev, pitch, cudaMemcpyDeviceToDevice, true, stream);
+}
+int b2c_engine_store_device(b2c_engine *e, uint8_t *dev, int64_t pitch, void *stream) {
+    return copy_block(e, dev, pitch, cudaMemcpyDeviceToDevice, false, stream);
+}
+
+int b2c_engine_exchange(b2c_engine *e, void *stream) {
+    if (!e) return B2C_EINVAL;
+    if (!e->any_nb) return B2C_OK;
+    if (!e->connected) {
+        set_error("engine_exchange: peers are not connected (import/connect_local first)");
+        return B2C_EINVAL;
+    }
+    CK(cudaSetDevice(e->device));
+    PushParams q;
+    fill_push_params(e, e->cur, false, q);
+    CK(launch_halo_push(q, (cudaStream_t)stream));
+    e->launches++;
+    e->epoch++;
+    return B2C_OK;
+}
+
+int b2c_engine_run(b2c_engine *e, int reps, void *stream) {
+    if (!e || reps < 0) return B2C_EINVAL;
+    CK(cudaSetDevice(e->device));
+    cudaStream_t s = (cudaStream_t)stream;
+    if (e->opts.boundary == B2C_CUDA_COMPAT) {
+        const int eff = 2 * (reps / 2);  // wrong-buffer copy-back of cuda_convolution.cu:93-97
+        for (int t = 0; t < eff; ++t) {
+            CK(launch_compat(e->cbuf[t & 1], e->cbuf[(t & 1) ^ 1], e->W, e->H, e->CH, s));
+            e->launches++;
+        }
+        e->iters_done = eff;
+        return B2C_OK;
+    }
+    if (e->any_nb && !e->connected) {
+        set_error("engine_run: peers are not connected");
+        return B2C_EINVAL;
+    }
+    if (e->any_nb && e->epoch == 0) {
+        set_error("engine_run: call b2c_engine_exchange after upload on every rank first");
+        return B2C_EINVAL;
+    }
+    const std::vector<Pass> passes = make_passes(e, reps);
+    e->iters_done = reps;
+    if (e->opts.check_every > 0) {
+        CK(cudaMemsetAsync(e->pad + kPadConverged, 0, 2 * sizeof(uint32_t), s));
+        e->last_passes = passes;
+        e->run_epoch0 = e->epoch;
+        e->run_cur0 = e->cur;
+        e->pending_converge_fixup = true;
+    }
+    bool graph = e->opts.use_graph == 1 || (e->opts.use_graph < 0 && passes.size() >= 8);
+    if (e->any_nb || e->opts.check_every > 0 || s == nullptr) graph = false;  // epochs are baked into params
+    if (graph) {
+        const auto key = std::make_pair(reps, e->cur);
+        auto it = e->graphs.find(key);
+        if (it == e->graphs.end()) {
+            const int cur0 = e->cur;
+            const long long l0 = e->launches, g0 = total_launches();
+            cudaGraph_t g;
+            CK(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
+            int rc = B2C_OK;
+            for (const Pass &ps : passes)
+                if ((rc = enqueue_pass(e, ps, s)) != B2C_OK) break;
+            cudaError_t ce = cudaStreamEndCapture(s, &g);
+            e->cur = cur0;
+            e->launches = l0;
+            count_launch(g0 - total_launches());  // captured, not launched
+            if (rc != B2C_OK) return rc;
+            CK(ce);
+            cudaGraphExec_t ge;
+            CK(cudaGraphInstantiate(&ge, g, 0));
+            cudaGraphDestroy(g);
+            it = e->graphs.emplace(key, ge).first;
+        }
+        CK(cudaGraphLaunch(it->second, s));
+        e->launches += (long long)passes.size();
+        count_launch((long long)passes.size());
+        e->cur ^= (int)(passes.size() & 1);
+        return B2C_OK;
+    }
+    for (const Pass &ps : passes) {
+        int rc = enqueue_pass(e, ps, s);
+        if (rc != B2C_OK) return rc;
+    }
+    return B2C_OK;
+}
+
+int b2c_engine_iterations_done(b2c_engine *e) {
+    if (!e) return B2C_EINVAL;
+    CK(cudaSetDevice(e->device));
+    CK(cudaDeviceSynchronize());
+    if (e->pending_converge_fixup) {
+        e->pending_converge_fixup = false;
+        uint32_t v[2] = {0, 0};
+        CK(cudaMemcpy(v, e->pad + kPadConverged, sizeof v, cudaMemcpyDeviceToHost));
+        if (v[0]) {
+            // Passes after the latch were skipped on every rank: rewind the host-side
+            // buffer index and epoch to the state right after the converging pass.
+            int cur = e->run_cur0;
+            uint32_t ep = e->run_epoch0;
+            for (const Pass &ps : e->last_passes) {
+                cur ^= 1;
+                if (e->any_nb) ep++;
+                if (ps.iters_after >= v[1]) break;
+            }
+            e->cur = cur;
+            e->epoch = ep;
+            e->iters_done = (int)v[1];
+        }
+    }
+    return e->iters_done;
+}
+
+int64_t b2c_engine_launches(const b2c_engine *e) { return e ? e->launches : 0; }
+
+int b2c_engine_describe(const b2c_engine *e, char *buf, size_t buflen) {
+    if (!e || !buf) return B2C_EINVAL;
+    const char *kn = e->kernel == B2C_KERNEL_NAIVE ? "naive" : (e->kernel == B2C_KERNEL_TMA ? "tma" : "stream");
+    if (e->opts.boundary == B2C_CUDA_COMPAT) {
+        snprintf(buf, buflen, "kernel=compat W=%d H=%d CH=%d", e->W, e->H, e->CH);
+        return B2C_OK;
+    }
+    const BandPlan bp = make_band_plan(e, e->K);
+    snprintf(buf, buflen,
+             "kernel=%s tb=%d strip=%dB block=%dx%d(bytes %d) pitch=%lld bands=%d(valid %dB) chunks=%d(x%d rows) "
+             "warps=%d halo_depth=%d fused_push=%d grid=%dx%d rank=%d",
+             kn, e->K, e->SB, e->R, e->C, e->bw, e->pitch, bp.nbands, bp.vw, bp.nchunks, bp.chunk_rows,
+             bp.nbands * bp.nchunks, e->any_nb ? e->F : 0, (e->any_nb && e->bw % e->SB == 0) ? 1 : 0, e->P, e->Q,
+             e->rank);
+    return B2C_OK;
+}
+
+int b2c_engine_set_delay(b2c_engine *e, int64_t cycles) {
+    if (!e) return B2C_EINVAL;
+    e->delay = cycles;
+    return B2C_OK;
+}
+
+int b2c_blur_device(const uint8_t *d_in, int64_t in_pitch, uint8_t *d_out, int64_t out_pitch, int W, int H,
+                    int CH, int reps, const b2c_opts *opts, void *stream) {
+    int dev = 0;
+    CK(cudaGetDevice(&dev));
+    b2c_engine *e = b2c_engine_create(dev, W, H, CH, 1, 1, 0, opts);
+    if (!e) return B2C_ECUDA;
+    int rc = b2c_engine_load_device(e, d_in, in_pitch, stream);
+    if (rc == B2C_OK) rc = b2c_engine_exchange(e, stream);
+    if (rc == B2C_OK) rc = b2c_engine_run(e, reps, stream);
+    if (rc == B2C_OK && e->opts.check_every > 0) rc = b2c_engine_iterations_done(e) < 0 ? B2C_ECUDA : B2C_OK;
+    if (rc == B2C_OK) rc = b2c_engine_store_device(e, d_out, out_pitch, stream);
+    if (rc == B2C_OK && cudaStreamSynchronize((cudaStream_t)stream) != cudaSuccess) rc = B2C_ECUDA;
+    b2c_engine_destroy(e);
+    return rc;
+}
+
+int b2c_stencil_step_device(const uint8_t *src, uint8_t *dst, int64_t pitch, int rows, int row_bytes, int ch,
+                            int filter, void *stream) {
+    if (!src || !dst || rows <= 0 || row_bytes <= 0 || (ch != 1 && ch != 3)) return B2C_EINVAL;
+    NaiveWeights w{};
+    const FilterDef &f = filter_def(filter);
+    for (int i = 0; i < 3; ++i)
+        for (int j = 0; j < 3; ++j) {
+            w.iw[i][j] = f.w[i][j];
+            w.fw[i][j] = (float)(f.w[i][j] / (double)f.den);
+        }
+    w.integer16 = f.den == 16;
+    CK(launch_naive(src, dst, pitch, rows, row_bytes, ch, w, (cudaStream_t)stream));
+    return B2C_OK;
+}
+
+int64_t b2c_total_launches(void) { return total_launches(); }
+
+}  // extern "C"

@@ -1,0 +1,248 @@
+// Kernel instantiations and launch dispatch for libb200conv_core (sm_100a).
+//   stream_kernel   : csrc/cuda/stencil_stream.cuh (the product path)
+//   naive_kernel    : one thread per output byte, any filter, any boundary —
+//                     the "minimum end-to-end slice" of SURVEY §7.3 step 2 and
+//                     the only path for BOX/EDGE (fp32, reference op order).
+//   compat kernels  : cuda/cuda_convolution.cu:9-47 observable semantics.
+//   halo_push_kernel: standalone ring -> neighbour-frame copy + epoch flags
+//                     (initial exchange, and the fallback when the block byte
+//                     width is not 16-byte aligned).
+#include <cuda_runtime.h>
+
+#include <atomic>
+
+#include "common.h"
+#include "kernels.h"
+#include "stencil_stream.cuh"
+
+namespace b2c {
+
+static std::atomic<long long> g_launches{0};
+long long total_launches() { return g_launches.load(); }
+void count_launch(long long n) { g_launches.fetch_add(n); }
+
+// ------------------------------------------------------------------ stream
+
+template <int K, int NW, int CH>
+static cudaError_t launch_stream_t(const PassParams &p, bool check, cudaStream_t s) {
+    const int warps = p.nbands * p.nchunks;
+    const int ctas = (warps + kWarpsPerCta - 1) / kWarpsPerCta;
+    if (check)
+        stream_kernel<K, NW, CH, true><<<ctas, kWarpsPerCta * 32, 0, s>>>(p);
+    else
+        stream_kernel<K, NW, CH, false><<<ctas, kWarpsPerCta * 32, 0, s>>>(p);
+    count_launch(1);
+    return cudaGetLastError();
+}
+
+template <int K, int NW>
+static cudaError_t launch_stream_ch(const PassParams &p, int ch, bool check, cudaStream_t s) {
+    return ch == 1 ? launch_stream_t<K, NW, 1>(p, check, s) : launch_stream_t<K, NW, 3>(p, check, s);
+}
+
+bool stream_config_ok(int k, int strip_bytes) {
+    if (strip_bytes != 4 && strip_bytes != 8 && strip_bytes != 16) return false;
+    if (k != 1 && k != 2 && k != 4 && k != 8) return false;
+    return k * (strip_bytes / 4) <= 16;  // register budget: 4 state registers per word per stage
+}
+
+cudaError_t launch_stream(const PassParams &p, int k, int strip_bytes, int ch, bool check, cudaStream_t s) {
+#define B2C_CASE(K_, NW_) \
+    if (k == K_ && strip_bytes == NW_ * 4) return launch_stream_ch<K_, NW_>(p, ch, check, s);
+    B2C_CASE(1, 1) B2C_CASE(2, 1) B2C_CASE(4, 1) B2C_CASE(8, 1)
+    B2C_CASE(1, 2) B2C_CASE(2, 2) B2C_CASE(4, 2) B2C_CASE(8, 2)
+    B2C_CASE(1, 4) B2C_CASE(2, 4) B2C_CASE(4, 4)
+#undef B2C_CASE
+    return cudaErrorInvalidValue;
+}
+
+// ------------------------------------------------------------------- naive
+
+// One iteration, one thread per output byte, on the engine's framed buffers.
+// ZERO/TORUS come from the frame contents (zero / pushed by the ring copy).
+template <bool INTEGER>
+__global__ void naive_kernel(const uint8_t *__restrict__ src, uint8_t *__restrict__ dst, long long pitch,
+                             int rows, int bw, int ch, NaiveWeights w) {
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;  // byte column -> threadIdx.x (coalesced)
+    const int r = blockIdx.y * blockDim.y + threadIdx.y;
+    if (x >= bw || r >= rows) return;
+    const uint8_t *p = src + (long long)r * pitch + x;
+    if (INTEGER) {
+        int acc = 0;
+#pragma unroll
+        for (int i = -1; i <= 1; ++i)
+#pragma unroll
+            for (int j = -1; j <= 1; ++j) acc += w.iw[i + 1][j + 1] * p[i * pitch + j * ch];
+        dst[(long long)r * pitch + x] = (uint8_t)(acc >> 4);
+    } else {
+        // fp32, row-major, multiply then add, no contraction: mpi_convolution.c:304-306
+        float acc = 0.0f;
+#pragma unroll
+        for (int i = -1; i <= 1; ++i)
+#pragma unroll
+            for (int j = -1; j <= 1; ++j)
+                acc = __fadd_rn(acc, __fmul_rn((float)p[i * pitch + j * ch], w.fw[i + 1][j + 1]));
+        dst[(long long)r * pitch + x] = (uint8_t)acc;  // cvt.rzi: truncation
+    }
+}
+
+cudaError_t launch_naive(const uint8_t *src, uint8_t *dst, long long pitch, int rows, int bw, int ch,
+                         const NaiveWeights &w, cudaStream_t s) {
+    dim3 block(128, 2), grid((bw + 127) / 128, (rows + 1) / 2);
+    if (w.integer16)
+        naive_kernel<true><<<grid, block, 0, s>>>(src, dst, pitch, rows, bw, ch, w);
+    else
+        naive_kernel<false><<<grid, block, 0, s>>>(src, dst, pitch, rows, bw, ch, w);
+    count_launch(1);
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------- cuda-compat
+
+// Grey: interior pixels only (guard of cuda_convolution.cu:17); the untouched
+// border of the two ping-pong buffers gives the frozen original/zero ring.
+__global__ void compat_grey_kernel(const uint8_t *__restrict__ src, uint8_t *__restrict__ dst, int W, int H) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    const int r = blockIdx.y * blockDim.y + threadIdx.y;
+    if (r < 1 || r >= H - 1 || c < 1 || c >= W - 1) return;
+    const uint8_t *p = src + (long long)r * W + c;
+    const int acc = p[-W - 1] + 2 * p[-W] + p[-W + 1] + 2 * p[-1] + 4 * p[0] + 2 * p[1] + p[W - 1] + 2 * p[W] + p[W + 1];
+    dst[(long long)r * W + c] = (uint8_t)(acc >> 4);
+}
+
+// RGB: the `y < 3W-3` guard (:34) makes it a stencil over the linear pixel
+// index p in [W+1, (H+1)W-4]; buffers carry two slack rows (the reference
+// reads/writes past its allocations there).
+__global__ void compat_rgb_kernel(const uint8_t *__restrict__ src, uint8_t *__restrict__ dst, int W,
+                                  long long b_lo, long long b_hi) {
+    const long long b = b_lo + (long long)blockIdx.x * blockDim.x + threadIdx.x;  // byte index
+    if (b > b_hi) return;
+    const long long pw = (long long)W * 3;
+    const uint8_t *p = src + b;
+    const int acc = p[-pw - 3] + 2 * p[-pw] + p[-pw + 3] + 2 * p[-3] + 4 * p[0] + 2 * p[3] + p[pw - 3] + 2 * p[pw] + p[pw + 3];
+    dst[b] = (uint8_t)(acc >> 4);
+}
+
+cudaError_t launch_compat(const uint8_t *src, uint8_t *dst, int W, int H, int ch, cudaStream_t s) {
+    if (ch == 1) {
+        if (H < 3 || W < 3) return cudaSuccess;
+        dim3 block(128, 2), grid((W + 127) / 128, (H + 1) / 2);
+        compat_grey_kernel<<<grid, block, 0, s>>>(src, dst, W, H);
+    } else {
+        if (H < 3 || W < 2) return cudaSuccess;
+        const long long b_lo = ((long long)W + 1) * 3, b_hi = ((long long)(H + 1) * W - 4) * 3 + 2;
+        const long long n = b_hi - b_lo + 1;
+        compat_rgb_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(src, dst, W, b_lo, b_hi);
+    }
+    count_launch(1);
+    return cudaGetLastError();
+}
+
+// --------------------------------------------------------------- halo push
+
+// One CTA per (direction, row slab).  Byte-exact copies (no alignment
+// assumptions), then the last CTA of a direction publishes the epoch.
+__global__ void halo_push_kernel(const PushParams q) {
+    const int d = blockIdx.y;
+    if (!q.peer_dst[d]) return;
+    if (q.wait_epoch_valid && threadIdx.x == 0) {
+        // Do not overwrite a frame the neighbour may still be reading.
+        const long long t0 = clock64();
+        while ((int)(ld_acquire_sys(q.flags + d * 32) - q.wait_epoch) < 0) {
+            if (clock64() - t0 > (20ll << 30)) {
+                printf("b200conv: halo push wait timeout dir=%d want=%u\n", d, q.wait_epoch);
+                __trap();
+            }
+        }
+    }
+    __syncthreads();
+    const int dr = kDirDrDev(d), dc = kDirDcDev(d);
+    const int F = q.depth;
+    const long long fb = (long long)F * q.ch;
+    const int sr0 = dr > 0 ? q.rows - F : 0, nr = dr ? F : q.rows;
+    const long long sc0 = dc > 0 ? q.bw - fb : 0, nc = dc ? fb : q.bw;
+    const int slabs = gridDim.x;
+    const int per = (nr + slabs - 1) / slabs;
+    const int r_lo = blockIdx.x * per, r_hi = min(nr, r_lo + per);
+    for (int r = r_lo; r < r_hi; ++r) {
+        const uint8_t *s = q.src + (long long)(sr0 + r) * q.pitch + sc0;
+        uint8_t *t = q.peer_dst[d] + (long long)(sr0 + r - dr * q.rows) * q.pitch + (sc0 - dc * (long long)q.bw);
+        const bool al = (((uintptr_t)s | (uintptr_t)t) & 15) == 0;
+        if (al) {
+            const long long n16 = nc / 16;
+            for (long long i = threadIdx.x; i < n16; i += blockDim.x)
+                __stcg(reinterpret_cast<uint4 *>(t) + i, __ldcg(reinterpret_cast<const uint4 *>(s) + i));
+            for (long long i = n16 * 16 + threadIdx.x; i < nc; i += blockDim.x) t[i] = s[i];
+        } else {
+            for (long long i = threadIdx.x; i < nc; i += blockDim.x) t[i] = s[i];
+        }
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned old = atomicAdd(q.counters + d * 32, 1u);
+        if (old + 1 == gridDim.x) {
+            q.counters[d * 32] = 0;
+            __threadfence_system();
+            st_release_sys(q.peer_flag[d], q.post_epoch);
+        }
+    }
+}
+
+cudaError_t launch_halo_push(const PushParams &q, cudaStream_t s) {
+    int slabs = (int)ceil_div(q.rows, 64);
+    if (slabs > 64) slabs = 64;
+    if (slabs < 1) slabs = 1;
+    halo_push_kernel<<<dim3(slabs, 8), 256, 0, s>>>(q);
+    count_launch(1);
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------- misc
+
+__global__ void set_u32_kernel(unsigned int *p, unsigned int v) { *p = v; }
+
+// Convergence bookkeeping after a CHECK pass: publish this rank's "changed"
+// bit to every rank, wait for all ranks' bits, and latch `converged` when the
+// OR is zero.  One thread; runs on the pass stream right after the CHECK pass.
+__global__ void converge_kernel(const ConvergeParams c) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    const unsigned mine = *c.changed;
+    *c.changed = 0;
+    // slot value = 2*seq + bit so that a slot from an older check never matches
+    const unsigned tag = c.seq * 2u;
+    for (int k = 0; k < c.nranks; ++k) {
+        __threadfence_system();
+        st_release_sys(c.peer_slots[k] + c.rank, tag | (mine ? 1u : 0u));
+    }
+    unsigned any = 0;
+    for (int k = 0; k < c.nranks; ++k) {
+        const long long t0 = clock64();
+        unsigned v;
+        while (((v = ld_acquire_sys(c.slots + k)) & ~1u) != tag) {
+            if (clock64() - t0 > (20ll << 30)) {
+                printf("b200conv: convergence wait timeout rank=%d peer=%d\n", c.rank, k);
+                __trap();
+            }
+        }
+        any |= v & 1u;
+    }
+    if (!any && !*c.converged) {
+        *c.converged = 1;
+        *c.converged_at = c.iters_after;
+    }
+}
+
+cudaError_t launch_converge(const ConvergeParams &c, cudaStream_t s) {
+    converge_kernel<<<1, 32, 0, s>>>(c);
+    count_launch(1);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_set_u32(unsigned int *p, unsigned int v, cudaStream_t s) {
+    set_u32_kernel<<<1, 1, 0, s>>>(p, v);
+    count_launch(1);
+    return cudaGetLastError();
+}
+
+}  // namespace b2c

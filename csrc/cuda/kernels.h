@@ -1,0 +1,56 @@
+// Host-visible launch interface of kernels.cu / stencil_tma.cu.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+
+namespace b2c {
+
+struct PassParams;
+
+struct NaiveWeights {
+    int iw[3][3];
+    float fw[3][3];
+    int integer16;
+};
+
+struct PushParams {
+    const uint8_t *src;      // interior origin of the buffer whose ring is pushed
+    long long pitch;
+    int rows, bw, ch, depth;
+    uint8_t *peer_dst[8];    // same buffer on the neighbour (interior origin) or null
+    uint32_t *peer_flag[8];
+    uint32_t *flags;
+    uint32_t *counters;
+    uint32_t post_epoch;
+    uint32_t wait_epoch;
+    int wait_epoch_valid;
+};
+
+struct ConvergeParams {
+    unsigned int *changed;        // this rank's OR-accumulated bit (reset here)
+    uint32_t *slots;              // our slot array, one word per rank
+    uint32_t *peer_slots[8];      // every rank's slot array (index = rank)
+    int nranks, rank;
+    unsigned int seq;             // check sequence number (>= 1)
+    unsigned int *converged;      // latched flag
+    unsigned int *converged_at;   // iterations completed when it latched
+    unsigned int iters_after;
+};
+
+__host__ __device__ inline int kDirDrDev(int d) { return d == 0 || d == 4 || d == 5 ? -1 : (d == 1 || d == 6 || d == 7 ? 1 : 0); }
+__host__ __device__ inline int kDirDcDev(int d) { return d == 2 || d == 4 || d == 6 ? -1 : (d == 3 || d == 5 || d == 7 ? 1 : 0); }
+
+bool stream_config_ok(int k, int strip_bytes);
+cudaError_t launch_stream(const PassParams &p, int k, int strip_bytes, int ch, bool check, cudaStream_t s);
+cudaError_t launch_naive(const uint8_t *src, uint8_t *dst, long long pitch, int rows, int bw, int ch,
+                         const NaiveWeights &w, cudaStream_t s);
+cudaError_t launch_compat(const uint8_t *src, uint8_t *dst, int W, int H, int ch, cudaStream_t s);
+cudaError_t launch_halo_push(const PushParams &q, cudaStream_t s);
+cudaError_t launch_converge(const ConvergeParams &c, cudaStream_t s);
+cudaError_t launch_set_u32(unsigned int *p, unsigned int v, cudaStream_t s);
+
+long long total_launches();
+void count_launch(long long n);
+
+}  // namespace b2c

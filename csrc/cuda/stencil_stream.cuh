@@ -1,0 +1,411 @@
+// Register-pipelined, temporally-blocked 3x3 binomial stencil for sm_100a.
+//
+// Replaces kernelConvolutionforGrey/RGB (cuda/cuda_convolution.cu:9-47) and the
+// per-iteration host loop (:66-87), and — with the halo block enabled — the
+// Isend/Irecv/Wait schedule of mpi/mpi_convolution.c:156-240.  Not a port: the
+// reference runs one thread per pixel with fp64 FMAs; here
+//
+//   * one warp streams a 32*SB-byte wide column band top to bottom; each lane
+//     owns an SB-byte strip (SB = 4/8/16) and keeps, for each of K fused
+//     iterations, two rows of separable partial sums in registers.  One HBM
+//     read + one HBM write per K iterations.
+//   * arithmetic is SIMD-within-register on 16-bit lanes: even bytes and odd
+//     bytes of a word live in two registers (E,O); the +-CH horizontal taps are
+//     the other-parity register of the same / adjacent word (a 16-bit funnel
+//     shift), so grey (CH=1) and rgb (CH=3) are one code path.
+//   * exact integer: out = (sum w*p) >> 4.  Lanes alternate between scale 1 and
+//     scale 16 from stage to stage so the >>4 is a single mask (even stages:
+//     v & 0x0FF0 == 16*floor(v/16)) or a single byte-permute (odd stages:
+//     high byte of the 16-bit lane); max lane value 16*4080 = 65280 fits.
+//   * left/right neighbours come from adjacent lanes by SHFL; the 32*SB window
+//     loses K*CH valid bytes per side (bands overlap by that much).
+//   * ZERO boundary: cells outside the global image are re-zeroed after every
+//     fused stage (warp-uniform EDGE variant, only for warps touching an edge).
+//   * multi-GPU: warps that own part of the block's boundary ring store those
+//     rows/strips straight into the neighbours' halo frames through peer
+//     (NVLink) pointers, then the last such warp per direction publishes an
+//     epoch flag with st.release.sys; consumers spin with ld.acquire.sys.
+//     Ring warps are scheduled first so the interior overlaps the transfer.
+#pragma once
+#include <cstdint>
+
+#include "b200conv.h"
+
+namespace b2c {
+
+constexpr int kFrameRows = 8;   // halo frame rows above/below the block (max K)
+constexpr int kLeftPad = 32;    // frame bytes left of the block, 16B multiple >= 8*3
+constexpr int kWarpsPerCta = 4;
+constexpr unsigned kFull = 0xffffffffu;
+
+struct HaloParams {
+    int enabled;            // any neighbour at all
+    int push;               // 1: push ring from this kernel (aligned fast path)
+    int depth;              // ring depth F (rows, and F*CH byte columns)
+    uint32_t wait_epoch;    // flags must be >= this before touching a frame
+    uint32_t post_epoch;    // value published after the pushes
+    uint8_t *peer_dst[8];   // neighbour's destination buffer, interior origin (or null)
+    uint32_t *peer_flag[8]; // neighbour's flag word that *we* write for direction d
+    uint32_t *flags;        // our flag words, index = direction the data came from
+    uint32_t *counters;     // our per-direction arrival counters
+    int expected[8];        // pusher warps per direction
+    int nbw, nbe;           // bands holding the west / east ring
+    long long delay;        // test hook: spin this many clocks before each wait
+};
+
+struct PassParams {
+    const uint8_t *src;  // interior origin of the source buffer
+    uint8_t *dst;        // interior origin of the destination buffer
+    long long pitch;
+    int rows;            // R
+    int bw;              // block byte width C*CH
+    int nbands, nchunks, chunk_rows;
+    int vw;              // valid bytes per band
+    int hlo;             // window bytes left of the valid band
+    int zero_n, zero_s, zero_w, zero_e;  // outside that side is outside the image (ZERO mode)
+    unsigned int *changed;  // CHECK: OR-accumulated "last stage changed a byte"
+    const unsigned int *converged;  // when set (non-null and non-zero) the pass is skipped
+    HaloParams halo;
+};
+
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t *p) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_sys(uint32_t *p, uint32_t v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+// Streaming loads/stores: L2 only, nothing is reused from L1.
+template <int NW>
+__device__ __forceinline__ void load_strip(const uint8_t *p, uint32_t (&w)[NW]) {
+    if constexpr (NW == 4) {
+        uint4 v = __ldcg(reinterpret_cast<const uint4 *>(p));
+        w[0] = v.x; w[1] = v.y; w[2] = v.z; w[3] = v.w;
+    } else if constexpr (NW == 2) {
+        uint2 v = __ldcg(reinterpret_cast<const uint2 *>(p));
+        w[0] = v.x; w[1] = v.y;
+    } else {
+        w[0] = __ldcg(reinterpret_cast<const uint32_t *>(p));
+    }
+}
+template <int NW>
+__device__ __forceinline__ void store_strip(uint8_t *p, const uint32_t (&w)[NW]) {
+    if constexpr (NW == 4) {
+        __stcg(reinterpret_cast<uint4 *>(p), make_uint4(w[0], w[1], w[2], w[3]));
+    } else if constexpr (NW == 2) {
+        __stcg(reinterpret_cast<uint2 *>(p), make_uint2(w[0], w[1]));
+    } else {
+        __stcg(reinterpret_cast<uint32_t *>(p), w[0]);
+    }
+}
+template <int NW>
+__device__ __forceinline__ void store_strip_partial(uint8_t *p, const uint32_t (&w)[NW], int nbytes) {
+#pragma unroll
+    for (int i = 0; i < NW; ++i)
+#pragma unroll
+        for (int b = 0; b < 4; ++b)
+            if (i * 4 + b < nbytes) p[i * 4 + b] = (uint8_t)(w[i] >> (8 * b));
+}
+
+// Horizontal 1-2-1 over byte stride CH on (E,O) 16-bit lanes.
+template <int NW, int CH>
+__device__ __forceinline__ void hsum(const uint32_t (&E)[NW], const uint32_t (&O)[NW],
+                                     uint32_t (&hE)[NW], uint32_t (&hO)[NW]) {
+    if constexpr (CH == 1) {
+        const uint32_t Op = __shfl_up_sync(kFull, O[NW - 1], 1);
+        const uint32_t En = __shfl_down_sync(kFull, E[0], 1);
+#pragma unroll
+        for (int i = 0; i < NW; ++i) {
+            const uint32_t ol = __funnelshift_l(i ? O[i - 1] : Op, O[i], 16);          // bytes -1, 1
+            const uint32_t er = __funnelshift_l(E[i], (i + 1 < NW) ? E[i + 1] : En, 16);  // bytes 2, 4
+            hE[i] = ol + 2u * E[i] + O[i];
+            hO[i] = E[i] + 2u * O[i] + er;
+        }
+    } else {
+        const uint32_t Op = __shfl_up_sync(kFull, O[NW - 1], 1);
+        const uint32_t Ep = __shfl_up_sync(kFull, E[NW - 1], 1);
+        const uint32_t On = __shfl_down_sync(kFull, O[0], 1);
+        const uint32_t En = __shfl_down_sync(kFull, E[0], 1);
+#pragma unroll
+        for (int i = 0; i < NW; ++i) {
+            const uint32_t op = i ? O[i - 1] : Op;                 // bytes -3, -1
+            const uint32_t ep = i ? E[i - 1] : Ep;
+            const uint32_t on = (i + 1 < NW) ? O[i + 1] : On;
+            const uint32_t en = (i + 1 < NW) ? E[i + 1] : En;     // bytes 4, 6
+            hE[i] = op + 2u * E[i] + __funnelshift_l(O[i], on, 16);   // bytes 3, 5
+            hO[i] = __funnelshift_l(ep, E[i], 16) + 2u * O[i] + en;   // bytes -2, 0
+        }
+    }
+}
+
+template <int K, int NW>
+struct PipeState {
+    uint32_t hE[K][NW], hO[K][NW];  // h of the previous input row, per stage
+    uint32_t sE[K][NW], sO[K][NW];  // h(r-2)+h(r-1), per stage
+};
+
+// One warp's stream.  EDGE: re-impose the ZERO boundary after every stage.
+template <int K, int NW, int CH, bool EDGE, bool CHECK>
+__device__ __forceinline__ void stream_band(const PassParams &p, const int band, const int chunk,
+                                            const int lane, const bool do_push,
+                                            const bool top, const bool bot, const bool west, const bool east) {
+    constexpr int SB = NW * 4;
+    const int x0 = band * p.vw - p.hlo;      // window start, block-local byte column
+    const int xs = x0 + lane * SB;           // this lane's strip
+    const int out_r0 = chunk * p.chunk_rows;
+    const int out_r1 = min(out_r0 + p.chunk_rows, p.rows);
+    const int in_r0 = out_r0 - K;
+    const int in_r1 = out_r1 + K;            // exclusive
+
+    // Which strips are stored.
+    const int band_lo = band * p.vw, band_hi = min(band_lo + p.vw, p.bw);
+    const bool st_any = xs >= band_lo && xs < band_hi;
+    const int st_bytes = st_any ? min(SB, p.bw - xs) : 0;  // SB = full strip
+
+    // Column masks (EDGE): lanes of bytes outside the image become 0.
+    uint32_t mE[NW], mO[NW];
+    if constexpr (EDGE) {
+#pragma unroll
+        for (int i = 0; i < NW; ++i) {
+            uint32_t me = 0, mo = 0;
+#pragma unroll
+            for (int b = 0; b < 4; ++b) {
+                const int c = xs + i * 4 + b;
+                const bool ok = (c >= 0 || !p.zero_w) && (c < p.bw || !p.zero_e);
+                const uint32_t m = ok ? (0xffffu << ((b >> 1) * 16)) : 0u;
+                if (b & 1) mo |= m; else me |= m;
+            }
+            mE[i] = me; mO[i] = mo;
+        }
+    }
+
+    PipeState<K, NW> st;
+#pragma unroll
+    for (int j = 0; j < K; ++j)
+#pragma unroll
+        for (int i = 0; i < NW; ++i) st.hE[j][i] = st.hO[j][i] = st.sE[j][i] = st.sO[j][i] = 0;
+
+    uint32_t chg = 0;
+    uint32_t pE[NW], pO[NW];  // CHECK: last stage's input lanes seen one step earlier
+    if constexpr (CHECK) {
+#pragma unroll
+        for (int i = 0; i < NW; ++i) pE[i] = pO[i] = 0;
+    }
+
+    const uint8_t *src = p.src + (long long)in_r0 * p.pitch + xs;
+    long long doff = (long long)(in_r0 - K) * p.pitch + xs;  // output row r-K for input row r
+
+    // Two rows of register prefetch.
+    uint32_t w0[NW], w1[NW];
+    load_strip<NW>(src, w0);
+    if (in_r0 + 1 < in_r1) load_strip<NW>(src + p.pitch, w1);
+    else {
+#pragma unroll
+        for (int i = 0; i < NW; ++i) w1[i] = 0;
+    }
+
+    for (int r = in_r0; r < in_r1; ++r, doff += p.pitch) {
+        uint32_t w[NW];
+#pragma unroll
+        for (int i = 0; i < NW; ++i) { w[i] = w0[i]; w0[i] = w1[i]; }
+        if (r + 2 < in_r1) load_strip<NW>(src + 2 * p.pitch, w1);
+        src += p.pitch;
+
+        uint32_t E[NW], O[NW];
+#pragma unroll
+        for (int i = 0; i < NW; ++i) {
+            E[i] = w[i] & 0x00ff00ffu;
+            O[i] = (w[i] >> 8) & 0x00ff00ffu;
+        }
+        uint32_t vE[NW], vO[NW];
+        uint32_t cE[NW], cO[NW];  // CHECK: row r-K of iteration K-1 (input of the last stage)
+#pragma unroll
+        for (int j = 0; j < K; ++j) {
+            if constexpr (CHECK) {
+                if (j == K - 1) {
+#pragma unroll
+                    for (int i = 0; i < NW; ++i) { cE[i] = pE[i]; cO[i] = pO[i]; pE[i] = E[i]; pO[i] = O[i]; }
+                }
+            }
+            uint32_t hE[NW], hO[NW];
+            hsum<NW, CH>(E, O, hE, hO);
+#pragma unroll
+            for (int i = 0; i < NW; ++i) {
+                const uint32_t se = st.hE[j][i] + hE[i], so = st.hO[j][i] + hO[i];
+                vE[i] = st.sE[j][i] + se;
+                vO[i] = st.sO[j][i] + so;
+                st.hE[j][i] = hE[i]; st.hO[j][i] = hO[i];
+                st.sE[j][i] = se;    st.sO[j][i] = so;
+            }
+            if (j + 1 < K) {
+                // stage j output = row r-j-1 after iteration j+1, kept as lanes for stage j+1
+#pragma unroll
+                for (int i = 0; i < NW; ++i) {
+                    if ((j & 1) == 0) {  // inputs had scale 1 -> lanes become 16*out
+                        E[i] = vE[i] & 0x0ff00ff0u;
+                        O[i] = vO[i] & 0x0ff00ff0u;
+                    } else {             // inputs had scale 16 -> the high byte of a lane is out
+                        E[i] = __byte_perm(vE[i], 0u, 0x4341);
+                        O[i] = __byte_perm(vO[i], 0u, 0x4341);
+                    }
+                }
+                if constexpr (EDGE) {
+                    const int srow = r - j - 1;
+                    const bool rok = (srow >= 0 || !p.zero_n) && (srow < p.rows || !p.zero_s);
+#pragma unroll
+                    for (int i = 0; i < NW; ++i) {
+                        E[i] = rok ? (E[i] & mE[i]) : 0u;
+                        O[i] = rok ? (O[i] & mO[i]) : 0u;
+                    }
+                }
+            }
+        }
+
+        // Final stage output: row r-K, packed back to bytes.
+        const int orow = r - K;
+        if (orow >= out_r0 && st_any) {
+            uint32_t o[NW];
+#pragma unroll
+            for (int i = 0; i < NW; ++i) {
+                if ((K - 1) & 1) o[i] = __byte_perm(vE[i], vO[i], 0x7351);
+                else o[i] = __byte_perm(vE[i] >> 4, vO[i] >> 4, 0x6240);
+            }
+            uint8_t *dst = p.dst + doff;
+            if (st_bytes == SB) store_strip<NW>(dst, o);
+            else store_strip_partial<NW>(dst, o, st_bytes);
+
+            if constexpr (CHECK) {
+#pragma unroll
+                for (int i = 0; i < NW; ++i) {
+                    // the last stage's input row, repacked to bytes (its lanes have scale 16 when K-1 is odd)
+                    const uint32_t q = ((K - 1) & 1) ? __byte_perm(cE[i] >> 4, cO[i] >> 4, 0x6240)
+                                                     : __byte_perm(cE[i], cO[i], 0x6240);
+                    uint32_t d = q ^ o[i];
+                    const int nb = st_bytes - i * 4;  // stored bytes of this word
+                    if (nb < 4) d &= nb <= 0 ? 0u : (0xffffffffu >> (8 * (4 - nb)));
+                    chg |= d;
+                }
+            }
+
+            if (do_push) {
+                const HaloParams &h = p.halo;
+                const int F = h.depth;
+                const long long up = (long long)p.rows * p.pitch, dn = -up;
+                const bool rt = orow < F, rb = orow >= p.rows - F;
+                const bool cw = xs < F * CH, ce = xs + SB > p.bw - F * CH;
+                if (top && rt && h.peer_dst[B2C_N]) store_strip<NW>(h.peer_dst[B2C_N] + doff + up, o);
+                if (bot && rb && h.peer_dst[B2C_S]) store_strip<NW>(h.peer_dst[B2C_S] + doff + dn, o);
+                if (west && cw) {
+                    if (h.peer_dst[B2C_W]) store_strip<NW>(h.peer_dst[B2C_W] + doff + p.bw, o);
+                    if (top && rt && h.peer_dst[B2C_NW]) store_strip<NW>(h.peer_dst[B2C_NW] + doff + up + p.bw, o);
+                    if (bot && rb && h.peer_dst[B2C_SW]) store_strip<NW>(h.peer_dst[B2C_SW] + doff + dn + p.bw, o);
+                }
+                if (east && ce) {
+                    if (h.peer_dst[B2C_E]) store_strip<NW>(h.peer_dst[B2C_E] + doff - p.bw, o);
+                    if (top && rt && h.peer_dst[B2C_NE]) store_strip<NW>(h.peer_dst[B2C_NE] + doff + up - p.bw, o);
+                    if (bot && rb && h.peer_dst[B2C_SE]) store_strip<NW>(h.peer_dst[B2C_SE] + doff + dn - p.bw, o);
+                }
+            }
+        }
+    }
+    if constexpr (CHECK) {
+        chg = __reduce_or_sync(kFull, chg);
+        if (lane == 0 && chg) atomicOr(p.changed, 1u);
+    }
+}
+
+// Ring-first work order: top chunk, bottom chunk, then the west/east bands of
+// the middle chunks, then the interior.
+__device__ __forceinline__ void map_work(int id, int NB, int NC, int nbw, int nbe, int &band, int &chunk) {
+    if (NC <= 2 || NB <= nbw + nbe) {  // everything is ring
+        chunk = id / NB; band = id % NB; return;
+    }
+    if (id < NB) { chunk = 0; band = id; return; }
+    id -= NB;
+    if (id < NB) { chunk = NC - 1; band = id; return; }
+    id -= NB;
+    const int side = nbw + nbe, mid = NC - 2;
+    if (id < side * mid) {
+        chunk = 1 + id / side;
+        const int s = id % side;
+        band = s < nbw ? s : NB - nbe + (s - nbw);
+        return;
+    }
+    id -= side * mid;
+    const int inner = NB - side;
+    chunk = 1 + id / inner;
+    band = nbw + id % inner;
+}
+
+template <int K, int NW, int CH, bool CHECK>
+__global__ void __launch_bounds__(kWarpsPerCta * 32)
+stream_kernel(const PassParams p) {
+    const int lane = threadIdx.x & 31;
+    const int wid = blockIdx.x * kWarpsPerCta + (threadIdx.x >> 5);
+    if (wid >= p.nbands * p.nchunks) return;
+    if (p.converged && *p.converged) return;  // fixed point already reached: nothing changes any more
+    int band, chunk;
+    map_work(wid, p.nbands, p.nchunks, p.halo.nbw, p.halo.nbe, band, chunk);
+
+    constexpr int SB = NW * 4;
+    const int x0 = band * p.vw - p.hlo;
+    const int in_r0 = chunk * p.chunk_rows - K;
+    const int in_r1 = min((chunk + 1) * p.chunk_rows, p.rows) + K;
+    const bool edge = (p.zero_w && x0 < 0) || (p.zero_e && x0 + 32 * SB > p.bw) ||
+                      (p.zero_n && in_r0 < 0) || (p.zero_s && in_r1 > p.rows);
+
+    bool top = false, bot = false, west = false, east = false;
+    const HaloParams &h = p.halo;
+    if (h.enabled) {
+        // ring membership, by the same formulas the host used for h.expected[]
+        top = chunk == 0; bot = chunk == p.nchunks - 1;
+        west = band < h.nbw; east = band >= p.nbands - h.nbe;
+        const bool dirs[8] = {top, bot, west, east, top && west, top && east, bot && west, bot && east};
+        if (top || bot || west || east) {
+            if (lane == 0) {
+                if (h.delay > 0) { const long long t0 = clock64(); while (clock64() - t0 < h.delay) {} }
+#pragma unroll
+                for (int d = 0; d < 8; ++d) {
+                    if (!dirs[d] || !h.peer_flag[d]) continue;
+                    const long long t0 = clock64();
+                    while ((int)(ld_acquire_sys(h.flags + d * 32) - h.wait_epoch) < 0) {
+                        if (clock64() - t0 > (20ll << 30)) {  // ~10 s: a peer died or the protocol broke
+                            printf("b200conv: halo wait timeout dir=%d want=%u have=%u\n", d, h.wait_epoch,
+                                   ld_acquire_sys(h.flags + d * 32));
+                            __trap();
+                        }
+                    }
+                }
+            }
+            __syncwarp();
+        }
+    }
+    const bool do_push = h.enabled && h.push && (top || bot || west || east);
+
+    if (edge) stream_band<K, NW, CH, true, CHECK>(p, band, chunk, lane, do_push, top, bot, west, east);
+    else      stream_band<K, NW, CH, false, CHECK>(p, band, chunk, lane, do_push, top, bot, west, east);
+
+    if (h.enabled && h.push && (top || bot || west || east)) {
+        // All of this warp's remote stores are issued; make them visible system-wide,
+        // then count in.  The last pusher per direction publishes the epoch.
+        __threadfence_system();
+        __syncwarp();
+        if (lane == 0) {
+            const bool dirs[8] = {top, bot, west, east, top && west, top && east, bot && west, bot && east};
+#pragma unroll
+            for (int d = 0; d < 8; ++d) {
+                if (!dirs[d] || !h.peer_flag[d]) continue;
+                const unsigned old = atomicAdd(h.counters + d * 32, 1u);
+                if ((int)old + 1 == h.expected[d]) {
+                    h.counters[d * 32] = 0;
+                    __threadfence_system();
+                    st_release_sys(h.peer_flag[d], h.post_epoch);
+                }
+            }
+        }
+    }
+}
+
+}  // namespace b2c

@@ -1,0 +1,227 @@
+/*
+ * b200conv — Blackwell-native iterative 3x3 image convolution engine.
+ *
+ * Public C ABI of libb200conv_core.so.  Everything the launcher, the PyTorch
+ * binding and ctypes users call goes through this header.  The library has no
+ * torch dependency.
+ *
+ * Reference parity notes cite files under /root/reference (the upstream
+ * theopaid/Parallel-Image-Convolution-using-MPI-OPENMP-and-CUDA tree).
+ */
+#ifndef B200CONV_H
+#define B200CONV_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ------------------------------------------------------------------ enums */
+
+/* Boundary semantics.
+ *  ZERO        : cells outside the image are 0 at every iteration
+ *                == mpi/mpi_convolution.c at one rank (calloc'd halo, :104-119).
+ *  TORUS       : indices wrap modulo H and W (README.md:63-66).
+ *  CUDA_COMPAT : cuda/cuda_convolution.cu semantics: interior-only update,
+ *                frozen 1-px border alternating original/zero, and the
+ *                odd-repetition copy-back bug (:93-97) => 2*floor(reps/2)
+ *                effective iterations.  RGB uses the linear-wrap model of the
+ *                buggy guard at :34. */
+enum { B2C_ZERO = 0, B2C_TORUS = 1, B2C_CUDA_COMPAT = 2 };
+
+/* Filter table of mpi/mpi_convolution.c:89-102.  Only GAUSSIAN is live in the
+ * reference; BOX (/9) and EDGE (/28) are the two commented-out alternatives. */
+enum { B2C_GAUSSIAN = 0, B2C_BOX = 1, B2C_EDGE = 2 };
+
+/* Neighbour directions, index into the 8-entry neighbour table. */
+enum { B2C_N = 0, B2C_S = 1, B2C_W = 2, B2C_E = 3, B2C_NW = 4, B2C_NE = 5, B2C_SW = 6, B2C_SE = 7 };
+
+/* Kernel families selectable through b2c_opts.kernel. */
+enum {
+    B2C_KERNEL_AUTO = 0,   /* pick by shape                                    */
+    B2C_KERNEL_NAIVE = 1,  /* one pass per iteration, byte-per-thread          */
+    B2C_KERNEL_STREAM = 2, /* register-pipelined temporal blocking, LDG feed   */
+    B2C_KERNEL_TMA = 3     /* same pipeline fed by TMA bulk-tensor tiles       */
+};
+
+/* Error codes (negative returns). */
+enum {
+    B2C_OK = 0,
+    B2C_EINVAL = -1,
+    B2C_ECUDA = -2,
+    B2C_EIO = -3,
+    B2C_ENOMEM = -4,
+    B2C_ETOOBIG = -5,
+    B2C_EDIVIDE = -6
+};
+
+const char *b2c_last_error(void);
+const char *b2c_version(void);
+
+/* ------------------------------------------------- decomposition (CPU, pure) */
+
+/* Same rule as RowsDivision() mpi/mpi_convolution.c:350-364: smallest block
+ * semi-perimeter among exact divisors, ties keep the smallest row count.
+ * Returns the number of process-grid rows, 0 when nothing divides. */
+int b2c_rows_division(int n_processes, int rows, int columns);
+
+/* P x Q grid for n ranks over an H x W image; returns B2C_EDIVIDE with the
+ * reference's "Cannot divide to processes" condition (:53-58). */
+int b2c_decompose(int n, int height, int width, int *grid_rows, int *grid_cols);
+
+/* 8-neighbour table of `rank` on a row-major P x Q grid (:72-73,142-149 only
+ * has N/S/W/E and never wraps).  Missing neighbour = -1.  TORUS wraps (a rank
+ * may be its own neighbour). */
+int b2c_neighbours(int rank, int grid_rows, int grid_cols, int boundary, int out[8]);
+
+/* ------------------------------------------------------------ CLI (CPU, pure) */
+
+typedef struct b2c_cli {
+    const char *image;  /* argv[1], not copied */
+    int width, height, repetitions;
+    int channels;       /* 1 = grey, 3 = rgb */
+    /* optional trailing flags (extensions; absent in the reference) */
+    int gpus;           /* 0 = all visible */
+    int boundary;       /* B2C_ZERO default */
+    int filter;         /* B2C_GAUSSIAN default */
+    int tb;             /* temporal-blocking depth, 0 = auto */
+    int kernel;         /* B2C_KERNEL_* */
+    int check_every;    /* convergence check period, 0 = off */
+    int checkpoint_every; /* write the image every N iterations, 0 = off */
+    int profile;        /* per-phase timings on stderr */
+    const char *json;   /* path for the JSON report, NULL = none */
+} b2c_cli;
+
+/* Grammar of Usage() mpi/mpi_convolution.c:328-348 and Initialization()
+ * cuda/functions.c:10-29: five positionals, argv[5] in {"grey","rgb"},
+ * atoi() for the numbers.  Returns B2C_OK or B2C_EINVAL. */
+int b2c_parse_cli(int argc, char **argv, b2c_cli *out);
+
+/* Writes the reference usage text.  style 0 = MPI program wording (:344),
+ * style 1 = CUDA program wording (functions.c:26). */
+int b2c_usage_text(const char *argv0, int style, char *buf, size_t buflen);
+
+/* "blur_" + argv[1] (whole string, like :244-246 / cuda/main.c:36-38). */
+int b2c_output_name(const char *image, char *buf, size_t buflen);
+
+/* ------------------------------------------------------------------ raw I/O */
+
+/* Read/write the R x C block at (row0, col0) of a headerless interleaved uint8
+ * W x H x CH image (mpi_convolution.c:126-140,244-262) with 64-bit offsets.
+ * `buf` rows are `pitch` bytes apart.  Returns bytes moved or a negative code.
+ * Short files are an error (the reference loops forever, functions.c:39-45). */
+int64_t b2c_read_block(const char *path, uint8_t *buf, int64_t pitch, int width, int height,
+                       int channels, int row0, int col0, int rows, int cols);
+int64_t b2c_write_block(const char *path, const uint8_t *buf, int64_t pitch, int width, int height,
+                        int channels, int row0, int col0, int rows, int cols, int create);
+
+/* ------------------------------------------------------------- CPU oracle */
+
+/* Integer oracle out = (sum w*p) >> 4 for GAUSSIAN, and the reference's fp32
+ * multiply-then-add order (mpi_convolution.c:301-322) for BOX/EDGE.  `in` and
+ * `out` are tightly packed H x W*CH; they may alias. */
+int b2c_oracle_blur(const uint8_t *in, uint8_t *out, int width, int height, int channels,
+                    int repetitions, int boundary, int filter);
+
+/* CPU emulation of the multi-rank halo protocol (same frames, epochs and
+ * 8-neighbour pushes as the GPU engine) on a P x Q grid with k-step passes.
+ * Result must equal b2c_oracle_blur on every grid (decomposition independence). */
+int b2c_oracle_blur_sharded(const uint8_t *in, uint8_t *out, int width, int height, int channels,
+                            int repetitions, int boundary, int grid_rows, int grid_cols, int tb);
+
+/* --------------------------------------------------------------- GPU engine */
+
+typedef struct b2c_opts {
+    int boundary;     /* B2C_ZERO / B2C_TORUS / B2C_CUDA_COMPAT */
+    int filter;       /* B2C_GAUSSIAN / B2C_BOX / B2C_EDGE       */
+    int kernel;       /* B2C_KERNEL_*                            */
+    int tb;           /* iterations fused per HBM pass (1,2,4,8); 0 = auto */
+    int strip_bytes;  /* bytes per thread per row (4,8,16); 0 = auto       */
+    int chunk_rows;   /* rows per warp stream; 0 = auto                    */
+    int use_graph;    /* capture the pass loop in a CUDA graph: -1 auto, 0, 1 */
+    int check_every;  /* fused convergence check period in iterations, 0 = off */
+} b2c_opts;
+
+void b2c_default_opts(b2c_opts *o);
+
+typedef struct b2c_engine b2c_engine;
+
+/* One engine = one rank's block on one device (cudaSetDevice is the caller's
+ * job only for single-rank use; the engine remembers `device`).
+ * Grid 1x1/rank 0 is the single-GPU case of cuda/cuda_convolution.cu:49-102.
+ * The engine owns two padded ping-pong buffers with a halo frame (the device
+ * analogue of the calloc'd (R+2)x(C+2) buffers, mpi_convolution.c:104-119). */
+b2c_engine *b2c_engine_create(int device, int width, int height, int channels, int grid_rows,
+                              int grid_cols, int rank, const b2c_opts *opts);
+void b2c_engine_destroy(b2c_engine *e);
+
+/* Geometry of this rank's block. */
+int b2c_engine_block(const b2c_engine *e, int *row0, int *col0, int *rows, int *cols);
+
+/* Peer wiring.  export: opaque bytes (cudaIpc handles for both buffers and the
+ * flag pad) to ship to the other ranks; import: all ranks' blobs in rank order.
+ * For ranks living in the same process, b2c_engine_connect_local wires raw
+ * pointers (used with cudaDeviceEnablePeerAccess, and by the one-GPU
+ * sequential multi-rank simulation in the tests). */
+#define B2C_HANDLE_BYTES 256
+int b2c_engine_export(b2c_engine *e, void *blob /* B2C_HANDLE_BYTES */);
+int b2c_engine_import(b2c_engine *e, const void *blobs /* n * B2C_HANDLE_BYTES */, int n);
+int b2c_engine_connect_local(b2c_engine **engines, int n);
+
+/* Data movement for this rank's block (tight or pitched host/device memory). */
+int b2c_engine_upload(b2c_engine *e, const uint8_t *host, int64_t pitch, void *stream);
+int b2c_engine_download(b2c_engine *e, uint8_t *host, int64_t pitch, void *stream);
+int b2c_engine_load_device(b2c_engine *e, const uint8_t *dev, int64_t pitch, void *stream);
+int b2c_engine_store_device(b2c_engine *e, uint8_t *dev, int64_t pitch, void *stream);
+
+/* Initial halo exchange (epoch 0) — call on every rank after upload, before run.
+ * No-op for a 1x1 ZERO/CUDA_COMPAT engine. */
+int b2c_engine_exchange(b2c_engine *e, void *stream);
+
+/* Run `repetitions` iterations on `stream` (asynchronous).  No MPI/NCCL/
+ * cudaMemcpyPeer inside: halos move by remote stores + release/acquire flags
+ * from inside the stencil kernel (replaces mpi_convolution.c:156-240). */
+int b2c_engine_run(b2c_engine *e, int repetitions, void *stream);
+
+/* Iterations actually executed by the last run (differs from `repetitions`
+ * only with CUDA_COMPAT odd counts or a convergence early-exit).  Synchronises. */
+int b2c_engine_iterations_done(b2c_engine *e);
+
+/* Kernel launches issued by this engine since creation. */
+int64_t b2c_engine_launches(const b2c_engine *e);
+/* Human-readable plan (kernel, tb, strip, chunks, grid) for reports. */
+int b2c_engine_describe(const b2c_engine *e, char *buf, size_t buflen);
+
+/* Test hook: busy-wait `cycles` SM clocks before every flag
+ * wait on this rank to shake out slot-reuse races. */
+int b2c_engine_set_delay(b2c_engine *e, int64_t cycles);
+
+/* ------------------------------------------------------- one-shot device API */
+
+/* Blur a tightly-or-pitched device image in one call (allocates the engine's
+ * scratch buffers internally, frees them before returning).  Single GPU. */
+int b2c_blur_device(const uint8_t *d_in, int64_t in_pitch, uint8_t *d_out, int64_t out_pitch,
+                    int width, int height, int channels, int repetitions, const b2c_opts *opts,
+                    void *stream);
+
+/* One plain iteration on caller-owned framed memory: `src`/`dst` point at the
+ * interior origin of buffers that have at least one halo row above/below and
+ * `channels` halo bytes left/right (the caller fills the halo, e.g. with NCCL
+ * send/recv — this is what the NCCL baseline uses).  Byte-per-thread kernel. */
+int b2c_stencil_step_device(const uint8_t *src, uint8_t *dst, int64_t pitch, int rows, int row_bytes,
+                            int channels, int filter, void *stream);
+
+/* Whole-program equivalent of cuda/main.c:10-53 (read file, blur, write
+ * blur_<name>) on one GPU; returns loop milliseconds in *loop_ms. */
+int b2c_blur_file(const char *image, int width, int height, int channels, int repetitions,
+                  const b2c_opts *opts, double *loop_ms, double *total_ms);
+
+/* Total kernel launches issued by the library in this process. */
+int64_t b2c_total_launches(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200CONV_H */

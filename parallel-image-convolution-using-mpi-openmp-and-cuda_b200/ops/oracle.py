@@ -1,0 +1,68 @@
+"""CPU oracles.
+
+``reference_oracle``  — the C++ oracle in ``csrc/core/oracle.cpp`` (integer for the Gaussian,
+                        fp32 reference op order for box/edge, zero/torus/cuda-compat boundaries).
+``numpy_oracle``      — an independent numpy restatement of ``out = (sum w*p) >> 4`` used to
+                        cross-check the C++ oracle (mpi/mpi_convolution.c:301-322 semantics at
+                        one rank; torus per README.md:63-66).
+``sharded_oracle``    — host emulation of the multi-rank frame/epoch halo protocol.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from .. import _lib
+from .._lib import BOUNDARY, FILTER, check, lib
+
+
+def _as_image(img):
+    """-> (contiguous uint8 ndarray [H, W*CH], W, H, CH, restore) for ndarray or torch input."""
+    torch_like = hasattr(img, "detach")
+    a = img.detach().cpu().numpy() if torch_like else np.asarray(img)
+    if a.dtype != np.uint8 or a.ndim not in (2, 3) or (a.ndim == 3 and a.shape[2] not in (1, 3)):
+        raise ValueError("image must be uint8 [H,W] or [H,W,3]")
+    ch = 1 if a.ndim == 2 else a.shape[2]
+    h, w = a.shape[0], a.shape[1]
+    flat = np.ascontiguousarray(a).reshape(h, w * ch)
+
+    def restore(out):
+        out = out.reshape(a.shape)
+        if torch_like:
+            import torch
+
+            return torch.from_numpy(out)
+        return out
+
+    return flat, w, h, ch, restore
+
+
+def reference_oracle(img, reps: int, boundary: str = "zero", filter: str = "gaussian"):
+    flat, w, h, ch, restore = _as_image(img)
+    out = np.empty_like(flat)
+    check(lib.b2c_oracle_blur(flat.ctypes.data, out.ctypes.data, w, h, ch, int(reps), BOUNDARY[boundary],
+                              FILTER[filter]), "oracle_blur")
+    return restore(out)
+
+
+def sharded_oracle(img, reps: int, grid, boundary: str = "zero", tb: int = 1):
+    flat, w, h, ch, restore = _as_image(img)
+    out = np.empty_like(flat)
+    check(lib.b2c_oracle_blur_sharded(flat.ctypes.data, out.ctypes.data, w, h, ch, int(reps), BOUNDARY[boundary],
+                                      int(grid[0]), int(grid[1]), int(tb)), "oracle_blur_sharded")
+    return restore(out)
+
+
+def numpy_oracle(img, reps: int, boundary: str = "zero"):
+    """Gaussian only.  Vectorised shifts on a padded int32 array; exact."""
+    flat, w, h, ch, restore = _as_image(img)
+    x = flat.reshape(h, w, ch).astype(np.int32)
+    mode = "wrap" if boundary == "torus" else "constant"
+    if boundary not in ("zero", "torus"):
+        raise ValueError("numpy_oracle supports zero/torus")
+    for _ in range(int(reps)):
+        p = np.pad(x, ((1, 1), (1, 1), (0, 0)), mode=mode)
+        hsum = p[:, :-2] + 2 * p[:, 1:-1] + p[:, 2:]
+        x = (hsum[:-2] + 2 * hsum[1:-1] + hsum[2:]) >> 4
+    return restore(x.astype(np.uint8).reshape(h, w * ch))

@@ -1,0 +1,84 @@
+"""All ranks of a grid inside ONE process — on one GPU (sequential emulation used by the
+tests) or on several GPUs with peer access.
+
+On a single GPU the ranks' kernels share the device, so a rank may never wait for a kernel
+that has not been launched yet: ``run`` therefore steps pass by pass over the ranks
+(every wait is already satisfied when its kernel starts).  With one GPU per rank the whole
+run of every rank is enqueued at once and the devices synchronise through the epoch flags.
+"""
+from __future__ import annotations
+
+import torch
+
+from ..ops.stencil import Engine
+from .decomposition import block_of
+
+
+class LocalGrid:
+    def __init__(self, width, height, channels, grid, devices=None, **opts):
+        self.width, self.height, self.channels = int(width), int(height), int(channels)
+        self.grid = (int(grid[0]), int(grid[1]))
+        n = self.grid[0] * self.grid[1]
+        self.devices = [torch.cuda.current_device()] * n if devices is None else list(devices)
+        self.multi_device = len(set(self.devices)) == n and n > 1
+        self.tb = int(opts.get("tb", 0)) or 4
+        self.engines = []
+        for k in range(n):
+            with torch.cuda.device(self.devices[k]):
+                self.engines.append(Engine(width, height, channels, grid=self.grid, rank=k,
+                                           device=self.devices[k], **opts))
+        if n > 1 or opts.get("boundary") == "torus":
+            Engine.connect_local(self.engines)
+
+    def close(self):
+        for e in self.engines:
+            e.close()
+
+    def _sync(self):
+        for d in set(self.devices):
+            torch.cuda.synchronize(d)
+
+    def load(self, img: torch.Tensor):
+        """Scatter a full image ([H,W] / [H,W,3] uint8, CPU or CUDA) to the ranks and exchange halos."""
+        for k, e in enumerate(self.engines):
+            r0, c0, r, c = block_of(k, self.grid, self.height, self.width)
+            with torch.cuda.device(self.devices[k]):
+                blk = img[r0:r0 + r, c0:c0 + c].contiguous()
+                if blk.is_cuda and blk.device.index != self.devices[k]:
+                    blk = blk.to(f"cuda:{self.devices[k]}")
+                e.load(blk)
+        self._sync()
+        for k, e in enumerate(self.engines):
+            with torch.cuda.device(self.devices[k]):
+                e.exchange()
+        self._sync()
+
+    def run(self, repetitions: int):
+        if self.multi_device:
+            for k, e in enumerate(self.engines):
+                with torch.cuda.device(self.devices[k]):
+                    e.run(repetitions)
+            return
+        left = int(repetitions)
+        step = max(1, self.tb)
+        if int(self.engines[0].opts.check_every) and len(self.engines) > 1:
+            # the cross-rank OR waits on every rank's kernel: impossible to emulate on one GPU
+            raise ValueError("check_every needs one GPU per rank")
+        while left > 0:
+            k = min(step, left)
+            for r, e in enumerate(self.engines):
+                with torch.cuda.device(self.devices[r]):
+                    e.run(k)
+            left -= k
+
+    def gather(self) -> torch.Tensor:
+        shape = (self.height, self.width) if self.channels == 1 else (self.height, self.width, self.channels)
+        out = torch.empty(shape, dtype=torch.uint8)
+        self._sync()
+        for k, e in enumerate(self.engines):
+            r0, c0, r, c = block_of(k, self.grid, self.height, self.width)
+            with torch.cuda.device(self.devices[k]):
+                blk = torch.empty(e.block_shape, dtype=torch.uint8, device=f"cuda:{self.devices[k]}")
+                e.store(blk)
+                out[r0:r0 + r, c0:c0 + c] = blk.cpu()
+        return out
