@@ -1,0 +1,294 @@
+#!/usr/bin/env python3
+"""Headline benchmark (BASELINE.json): gigapixel-iterations/second, device-timed, max over ranks.
+
+Default config = BASELINE.json config 3: 16384x16384 rgb, 1000 repetitions, strong-scaled
+over N GPUs on the reference's RowsDivision grid.  One *step* = one full
+``repetitions``-iteration blur of the whole image (what one run of the reference program does).
+
+  python bench.py --gpus 1 --steps 3 --warmup 3
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
+         --master-port P bench.py --gpus N --steps K --warmup W
+  python bench.py --impl reference ...     # the unmodified reference CUDA program (baseline/_ref)
+
+Prints ONE JSON line on rank 0.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import re
+import subprocess
+import sys
+import tempfile
+import time
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+# best published single-GPU CUDA rate of the reference (GTX 970, marginal
+# kernel rate from the README.pdf p.7 table): 0.225 Gpix-it/s rgb, 3.14 Gpix-it/s grey.
+PUBLISHED = {"rgb": 0.225, "grey": 3.14}
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200conv", choices=["b200conv", "reference"])
+    ap.add_argument("--width", type=int, default=16384)
+    ap.add_argument("--height", type=int, default=16384)
+    ap.add_argument("--color", default="rgb", choices=["grey", "rgb"])
+    ap.add_argument("--reps", type=int, default=1000)
+    ap.add_argument("--boundary", default="zero", choices=["zero", "torus"])
+    ap.add_argument("--tb", type=int, default=0)
+    ap.add_argument("--strip", type=int, default=0)
+    ap.add_argument("--chunk-rows", type=int, default=0)
+    ap.add_argument("--kernel", default="auto")
+    ap.add_argument("--check-every", type=int, default=0)
+    ap.add_argument("--weak", action="store_true", help="keep --width x --height per GPU (weak scaling)")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def weak_shape(n, w, h):
+    """Per-GPU block w x h -> whole image, on the grid RowsDivision picks."""
+    shapes = {1: (1, 1), 2: (1, 2), 4: (2, 2), 8: (2, 4)}
+    p, q = shapes.get(n, (1, n))
+    return w * q, h * p
+
+
+# --------------------------------------------------------------------------- own arm
+
+def run_b200conv(a):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    import b200conv
+    from b200conv.utils.clocks import ClockSampler
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != a.gpus:
+        if world == 1 and a.gpus > 1:
+            raise SystemExit("launch with torch.distributed.run --nproc-per-node N for --gpus N")
+        a.gpus = world
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
+    W, H = (weak_shape(world, a.width, a.height) if a.weak else (a.width, a.height))
+    ch = 3 if a.color == "rgb" else 1
+    opts = dict(boundary=a.boundary, tb=a.tb, strip_bytes=a.strip, chunk_rows=a.chunk_rows, kernel=a.kernel,
+                check_every=a.check_every)
+
+    if world > 1:
+        eng = b200conv.ShardedBlur(W, H, ch, device=local, **opts)
+        core = eng.engine
+    else:
+        core = b200conv.Engine(W, H, ch, device=local, **opts)
+        eng = None
+    shape = core.block_shape
+    # synthetic random block in pinned host memory (no dataset exists: the reference ships no image)
+    rng = np.random.default_rng(1234 + rank)
+    host_in = torch.empty(shape, dtype=torch.uint8).pin_memory()
+    host_in.numpy()[...] = rng.integers(0, 256, size=shape, dtype=np.uint8)
+    host_out = torch.empty(shape, dtype=torch.uint8).pin_memory()
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def load():
+        if eng is not None:
+            eng.load(host_in)
+        else:
+            core.load(host_in)
+            core.exchange()
+
+    def max_over_ranks(x):
+        t = torch.tensor([x], dtype=torch.float64, device=f"cuda:{local}")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum_over_ranks(x):
+        t = torch.tensor([x], dtype=torch.float64, device=f"cuda:{local}")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    # ---- device-timed loop: K steps of `reps` iterations on resident data
+    load()
+    for _ in range(a.warmup):
+        core.run(a.reps)
+    barrier()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    l0 = b200conv.total_launches()
+    sampler = ClockSampler(local) if rank == 0 else None
+    if sampler:
+        sampler.__enter__()
+    wall0 = time.perf_counter()
+    ev0.record()
+    for _ in range(a.steps):
+        core.run(a.reps)
+    ev1.record()
+    barrier()
+    wall = time.perf_counter() - wall0
+    if sampler:
+        sampler.__exit__()
+    ms = max_over_ranks(ev0.elapsed_time(ev1)) / a.steps
+    launches = int(sum_over_ranks(b200conv.total_launches() - l0))
+    iters_done = core.iterations_done() if a.check_every else a.reps
+    value = W * H * iters_done / (ms * 1e-3) / 1e9
+
+    # ---- end to end through the public API: H2D of the step's input from pinned memory,
+    #      the iterations, D2H of the result, every step
+    e2e = None
+    if not a.no_e2e:
+        def step():
+            load()
+            core.run(a.reps)
+            if a.check_every:
+                core.iterations_done()
+            core.store(host_out)
+
+        for _ in range(max(1, min(a.warmup, 2))):
+            step()
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.perf_counter()
+        e0.record()
+        for _ in range(a.steps):
+            step()
+        e1.record()
+        barrier()
+        e2e_wall = (time.perf_counter() - t0) / a.steps
+        e2e_ms = max(max_over_ranks(e0.elapsed_time(e1)) / a.steps, 0.0)
+        nbytes = int(host_in.numel())
+        e2e = {"value": W * H * iters_done / (e2e_ms * 1e-3) / 1e9, "unit": "Gpix-it/s",
+               "ms_per_step": e2e_ms, "wall_ms_per_step": max_over_ranks(e2e_wall * 1e3),
+               "h2d_bytes_per_step": nbytes * world, "d2h_bytes_per_step": nbytes * world}
+
+    desc = core.describe()
+    if rank == 0:
+        grid = core.grid
+        roof = 6555.5e9 / 2 / ch / 1e9 * world  # k=1 HBM roofline, MEASURED_PEAKS.json copy bandwidth
+        try:
+            peaks = json.loads((ROOT / "MEASURED_PEAKS.json").read_text())
+            roof = peaks["hbm_gbs"] / 2 / ch * world
+        except Exception:
+            pass
+        out = {
+            "metric": "gigapixel-iterations/sec (device-timed, max over ranks)",
+            "value": value, "unit": "Gpix-it/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
+            "ms_per_step": ms, "higher_is_better": True, "scaling": "weak" if a.weak else "strong",
+            "vs_baseline": value / PUBLISHED[a.color], "dtype": "uint8 (exact integer; reference computes in fp32/fp64)",
+            "data": "synthetic random uint8 image, generated per rank in pinned host memory",
+            "impl": "b200conv",
+            "config": {"model": f"3x3 gaussian blur {W}x{H} {a.color}", "width": W, "height": H, "color": a.color,
+                       "repetitions": a.reps, "iterations_done": iters_done, "boundary": a.boundary,
+                       "global_batch": 1, "parallelism": f"2d-block {grid[0]}x{grid[1]}",
+                       "l2_policy": f"image {W * H * ch / world / 1e6:.0f} MB per GPU per buffer vs 126 MB L2"
+                                    + (" (larger than L2)" if W * H * ch / world > 126e6 else
+                                       " (fits in L2: resident by design, see DESIGN.md)"),
+                       "plan": desc},
+            "pct_hbm_roofline_k1": 100.0 * value / roof,
+            "gpu_launches": launches, "wall_s_timed_region": wall,
+            "clocks": sampler.summary() if sampler else None,
+            "e2e": e2e,
+        }
+        print(json.dumps(out), flush=True)
+    if eng is not None:
+        eng.close()
+        dist.destroy_process_group()
+    else:
+        core.close()
+
+
+# --------------------------------------------------------------------- reference arm
+
+def run_reference(a):
+    """The unmodified reference CUDA program (baseline/_ref/cuda, its own Makefile), run the
+    way its README says: ``./cuda_convolution image W H reps rgb|grey``.  It is a single-GPU
+    program, so for --gpus N > 1 it still runs on one GPU (rank 0); other ranks exit."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    sys.path.insert(0, str(ROOT / "baseline"))
+    import install_ref
+
+    exe = ROOT / "baseline" / "_ref" / "cuda" / "cuda_convolution"
+    try:
+        if not exe.exists():
+            install_ref.copy_tree()
+            rc, log = install_ref.build_cuda()
+            if rc or not exe.exists():
+                raise RuntimeError("reference cuda build failed: " + log.strip().splitlines()[-1][:200])
+    except Exception as e:  # noqa: BLE001
+        print(json.dumps({"impl": "reference", "unavailable": str(e)[:300]}))
+        return
+    import numpy as np
+
+    W, H = (weak_shape(a.gpus, a.width, a.height) if a.weak else (a.width, a.height))
+    ch = 3 if a.color == "rgb" else 1
+    if W * H * ch >= 2 ** 31:
+        print(json.dumps({"impl": "reference", "unavailable":
+                          f"image is {W * H * ch} bytes; the reference computes sizes in int (cuda/main.c:27)"}))
+        return
+    tmp = Path(tempfile.mkdtemp(prefix="b2c_ref_", dir=os.environ.get("TMPDIR", "/tmp")))
+    img = tmp / "bench.raw"
+    rng = np.random.default_rng(1234)
+    with open(img, "wb") as f:
+        rows = max(1, (64 << 20) // (W * ch))
+        for r in range(0, H, rows):
+            f.write(rng.integers(0, 256, size=(min(rows, H - r), W * ch), dtype=np.uint8).tobytes())
+    times, fail = [], None
+    env = dict(os.environ, CUDA_VISIBLE_DEVICES=os.environ.get("CUDA_VISIBLE_DEVICES", "0").split(",")[0])
+    wall0 = time.perf_counter()
+    for i in range(a.warmup + a.steps):
+        p = subprocess.run([str(exe), "bench.raw", str(W), str(H), str(a.reps), a.color], cwd=tmp, env=env,
+                           capture_output=True, text=True)
+        m = re.search(r"Execution time: ([0-9.]+) sec", p.stdout)
+        if p.returncode != 0 or not m:
+            fail = (p.stderr.strip() or p.stdout.strip() or f"exit {p.returncode}")[:300]
+            break
+        if i >= a.warmup:
+            times.append(float(m.group(1)))
+    wall = time.perf_counter() - wall0
+    for f in tmp.iterdir():
+        f.unlink()
+    tmp.rmdir()
+    if fail is not None:
+        print(json.dumps({"impl": "reference", "unavailable": f"reference program failed: {fail}"}))
+        return
+    sec = sum(times) / len(times)
+    iters = 2 * (a.reps // 2)  # cuda_convolution.cu:93-97 copies back the wrong buffer for odd counts
+    value = W * H * a.reps / sec / 1e9
+    print(json.dumps({
+        "metric": "gigapixel-iterations/sec", "value": value, "unit": "Gpix-it/s", "n_gpus": a.gpus,
+        "steps": a.steps, "warmup": a.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True,
+        "scaling": "weak" if a.weak else "strong", "vs_baseline": value / PUBLISHED[a.color],
+        "dtype": "uint8 in/out, fp32+fp64 arithmetic", "data": "synthetic random uint8 .raw file",
+        "impl": "reference",
+        "config": {"model": f"3x3 gaussian blur {W}x{H} {a.color}", "width": W, "height": H, "color": a.color,
+                   "repetitions": a.reps, "effective_iterations": iters,
+                   "parallelism": "single GPU (the reference CUDA program cannot use more)",
+                   "timer": "the program's own 'Execution time' line: file read + cudaMalloc + H2D + kernels + "
+                            "D2H + file write (cuda/main.c:20-47); PTX JIT of its sm_52 build on B200"},
+        "gpus_used": 1, "wall_s_timed_region": wall,
+        "e2e": {"value": value, "unit": "Gpix-it/s", "h2d_bytes_per_step": W * H * ch, "d2h_bytes_per_step": W * H * ch},
+    }))
+
+
+if __name__ == "__main__":
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200conv(args)

@@ -98,38 +98,53 @@ struct b2c_engine {
     std::map<std::pair<int, int>, cudaGraphExec_t> graphs;
     NaiveWeights nw{};
     TmaState *tma = nullptr;
+    mutable BandPlan plan_cache[9];
+    mutable bool plan_ok[9] = {false, false, false, false, false, false, false, false, false};
 };
 
 namespace {
 
 BandPlan make_band_plan(const b2c_engine *e, int k) {
+    if (k >= 1 && k <= 8 && e->plan_ok[k]) return e->plan_cache[k];
     BandPlan bp{};
     const int SB = e->SB, CH = e->CH;
-    bp.hlo = (int)round_up((long long)k * CH, SB);
-    bp.vw = (int)round_down(32 * SB - bp.hlo - k * CH, SB);
+    // window start and band pitch: strip-aligned for per-lane LDGs, 16 B for TMA box origins
+    const int align = e->kernel == B2C_KERNEL_TMA ? 16 : SB;
+    bp.hlo = (int)round_up((long long)k * CH, align);
+    bp.vw = (int)round_down(32 * SB - bp.hlo - k * CH, align);
     bp.nbands = (int)ceil_div(e->bw, bp.vw);
-    // rows per warp: enough warps for ~2 waves of 16 warps/SM, but keep the 2k-row
-    // pipeline fill below ~12% of a chunk.
-    const long long target = (long long)e->sm_count * 32;
+    // Rows per warp.  All warps cost the same, so the grid is sized to whole waves of
+    // resident warps (occupancy x SMs): a partial last wave would idle most of the chip.
     int chunk_rows = e->opts.chunk_rows;
     if (chunk_rows <= 0) {
-        long long want = std::max<long long>(1, target / bp.nbands);
-        chunk_rows = (int)ceil_div(e->R, want);
-        chunk_rows = std::max(chunk_rows, std::max(16 * k, 32));
+        int occ = e->kernel == B2C_KERNEL_TMA ? stream_tma_occupancy(k, SB, CH) : stream_occupancy(k, SB, CH);
+        if (occ <= 0) occ = 4;
+        const long long wave = (long long)e->sm_count * occ * kWarpsPerCta;  // warps resident at once
+        // Measured on B200 (profiles/tuning.md): many short streams beat one wave of long
+        // ones — CTAs finish at different times and the block scheduler back-fills — until
+        // the 2k-row pipeline fill per chunk starts to cost.  Aim for >= 4 waves of warps
+        // with 128..256-row chunks; never below 8k rows (fill <= 25 %).
+        const int min_rows = std::max(8 * k, 32);
+        long long cr = (long long)e->R * bp.nbands / (4 * wave);
+        cr = std::max<long long>(min_rows, std::min<long long>(cr, 256));
+        if (cr > 128 && (long long)bp.nbands * ceil_div(e->R, 128) <= 8 * wave) cr = 128;
+        cr = std::max<long long>(cr, min_rows);
+        const int nc = (int)ceil_div(e->R, cr);
+        chunk_rows = (int)ceil_div(e->R, nc);
     }
     chunk_rows = std::max(chunk_rows, e->F);
     chunk_rows = std::min(chunk_rows, std::max(e->R, 1));
     chunk_rows = std::max(chunk_rows, 1);
     bp.chunk_rows = chunk_rows;
     bp.nchunks = (int)ceil_div(e->R, chunk_rows);
-    // re-balance so the last chunk is not a sliver
-    bp.chunk_rows = (int)ceil_div(e->R, bp.nchunks);
-    if (bp.chunk_rows < e->F) bp.chunk_rows = std::min(e->F, e->R);
-    bp.nchunks = (int)ceil_div(e->R, bp.chunk_rows);
     const int fb = e->F * CH;
     bp.nbw = std::min(bp.nbands, (int)ceil_div(fb, bp.vw));
     bp.nbe = bp.nbands - (int)(std::max(0, e->bw - fb) / bp.vw);
     bp.nbe = std::max(1, std::min(bp.nbands, bp.nbe));
+    if (k >= 1 && k <= 8) {
+        e->plan_cache[k] = bp;
+        e->plan_ok[k] = true;
+    }
     return bp;
 }
 
@@ -151,6 +166,10 @@ void fill_pass_params(const b2c_engine *e, int k, bool check, int src_i, PassPar
     p.zero_s = zero && e->nb[B2C_S] < 0;
     p.zero_w = zero && e->nb[B2C_W] < 0;
     p.zero_e = zero && e->nb[B2C_E] < 0;
+    {
+        static const int pf = getenv("B200CONV_PF") ? atoi(getenv("B200CONV_PF")) : 0;
+        p.pf_rows = pf;
+    }
     p.changed = check ? e->pad + kPadChanged : nullptr;
     p.converged = e->opts.check_every > 0 ? e->pad + kPadConverged : nullptr;
     HaloParams &h = p.halo;
@@ -283,7 +302,6 @@ void choose_plan(b2c_engine *e) {
         }
     }
     while (K * (SB / 4) > 16) SB >>= 1;
-    if (e->kernel == B2C_KERNEL_TMA) SB = 16;
     e->K = K;
     e->SB = SB;
     e->F = e->any_nb ? K : 1;

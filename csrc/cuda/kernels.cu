@@ -23,21 +23,28 @@ void count_launch(long long n) { g_launches.fetch_add(n); }
 
 // ------------------------------------------------------------------ stream
 
+// op 0: launch, op 1: occupancy query (resident CTAs per SM) returned through *occ.
 template <int K, int NW, int CH>
-static cudaError_t launch_stream_t(const PassParams &p, bool check, cudaStream_t s) {
-    const int warps = p.nbands * p.nchunks;
+static cudaError_t stream_op_t(int op, const PassParams *p, bool check, cudaStream_t s, int *occ) {
+    auto fn = check ? stream_kernel<K, NW, CH, true> : stream_kernel<K, NW, CH, false>;
+    if (op == 1) return cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, fn, kWarpsPerCta * 32, 0);
+    const int warps = p->nbands * p->nchunks;
     const int ctas = (warps + kWarpsPerCta - 1) / kWarpsPerCta;
-    if (check)
-        stream_kernel<K, NW, CH, true><<<ctas, kWarpsPerCta * 32, 0, s>>>(p);
-    else
-        stream_kernel<K, NW, CH, false><<<ctas, kWarpsPerCta * 32, 0, s>>>(p);
+    fn<<<ctas, kWarpsPerCta * 32, 0, s>>>(*p);
     count_launch(1);
     return cudaGetLastError();
 }
 
-template <int K, int NW>
-static cudaError_t launch_stream_ch(const PassParams &p, int ch, bool check, cudaStream_t s) {
-    return ch == 1 ? launch_stream_t<K, NW, 1>(p, check, s) : launch_stream_t<K, NW, 3>(p, check, s);
+static cudaError_t stream_op(int op, const PassParams *p, int k, int strip_bytes, int ch, bool check, cudaStream_t s,
+                             int *occ) {
+#define B2C_CASE(K_, NW_)                                                              \
+    if (k == K_ && strip_bytes == NW_ * 4)                                             \
+        return ch == 1 ? stream_op_t<K_, NW_, 1>(op, p, check, s, occ) : stream_op_t<K_, NW_, 3>(op, p, check, s, occ);
+    B2C_CASE(1, 1) B2C_CASE(2, 1) B2C_CASE(4, 1) B2C_CASE(8, 1)
+    B2C_CASE(1, 2) B2C_CASE(2, 2) B2C_CASE(4, 2) B2C_CASE(8, 2)
+    B2C_CASE(1, 4) B2C_CASE(2, 4) B2C_CASE(4, 4)
+#undef B2C_CASE
+    return cudaErrorInvalidValue;
 }
 
 bool stream_config_ok(int k, int strip_bytes) {
@@ -47,13 +54,16 @@ bool stream_config_ok(int k, int strip_bytes) {
 }
 
 cudaError_t launch_stream(const PassParams &p, int k, int strip_bytes, int ch, bool check, cudaStream_t s) {
-#define B2C_CASE(K_, NW_) \
-    if (k == K_ && strip_bytes == NW_ * 4) return launch_stream_ch<K_, NW_>(p, ch, check, s);
-    B2C_CASE(1, 1) B2C_CASE(2, 1) B2C_CASE(4, 1) B2C_CASE(8, 1)
-    B2C_CASE(1, 2) B2C_CASE(2, 2) B2C_CASE(4, 2) B2C_CASE(8, 2)
-    B2C_CASE(1, 4) B2C_CASE(2, 4) B2C_CASE(4, 4)
-#undef B2C_CASE
-    return cudaErrorInvalidValue;
+    return stream_op(0, &p, k, strip_bytes, ch, check, s, nullptr);
+}
+
+int stream_occupancy(int k, int strip_bytes, int ch) {
+    int occ = 0;
+    if (stream_op(1, nullptr, k, strip_bytes, ch, false, nullptr, &occ) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return occ;
 }
 
 // ------------------------------------------------------------------- naive

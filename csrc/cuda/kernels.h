@@ -42,6 +42,7 @@ __host__ __device__ inline int kDirDrDev(int d) { return d == 0 || d == 4 || d =
 __host__ __device__ inline int kDirDcDev(int d) { return d == 2 || d == 4 || d == 6 ? -1 : (d == 3 || d == 5 || d == 7 ? 1 : 0); }
 
 bool stream_config_ok(int k, int strip_bytes);
+int stream_occupancy(int k, int strip_bytes, int ch);  // resident CTAs (of kWarpsPerCta warps) per SM
 cudaError_t launch_stream(const PassParams &p, int k, int strip_bytes, int ch, bool check, cudaStream_t s);
 cudaError_t launch_naive(const uint8_t *src, uint8_t *dst, long long pitch, int rows, int bw, int ch,
                          const NaiveWeights &w, cudaStream_t s);

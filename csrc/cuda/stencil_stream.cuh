@@ -28,14 +28,18 @@
 //     Ring warps are scheduled first so the interior overlaps the transfer.
 #pragma once
 #include <cstdint>
+#include <type_traits>
 
 #include "b200conv.h"
 
 namespace b2c {
 
-constexpr int kFrameRows = 8;   // halo frame rows above/below the block (max K)
+constexpr int kFrameRows = 12;  // halo frame rows above/below the block: max K (8) + the 3x loop overrun + slack
 constexpr int kLeftPad = 32;    // frame bytes left of the block, 16B multiple >= 8*3
 constexpr int kWarpsPerCta = 4;
+#ifndef B2C_MIN_CTAS
+#define B2C_MIN_CTAS 4   // resident CTAs per SM the register allocator must allow (<= 128 regs/thread)
+#endif
 constexpr unsigned kFull = 0xffffffffu;
 
 struct HaloParams {
@@ -65,6 +69,7 @@ struct PassParams {
     int zero_n, zero_s, zero_w, zero_e;  // outside that side is outside the image (ZERO mode)
     unsigned int *changed;  // CHECK: OR-accumulated "last stage changed a byte"
     const unsigned int *converged;  // when set (non-null and non-zero) the pass is skipped
+    int pf_rows;         // rows ahead to prefetch into L2 (0 = off)
     HaloParams halo;
 };
 
@@ -109,46 +114,64 @@ __device__ __forceinline__ void store_strip_partial(uint8_t *p, const uint32_t (
             if (i * 4 + b < nbytes) p[i * 4 + b] = (uint8_t)(w[i] >> (8 * b));
 }
 
-// Horizontal 1-2-1 over byte stride CH on (E,O) 16-bit lanes.
+// Horizontal 1-2-1 over byte stride CH on (E,O) 16-bit lanes, as two pairwise sums
+//   t[x] = p[x] + p[x+CH],   h[x] = t[x-CH] + t[x]
+// (4 adds per word instead of 6).  CH is odd, so a tap always lives in the other-parity
+// register: either that register itself or a 16-bit funnel shift of two neighbours
+// (ptxas folds shift+add into one LEA.HI).  Lane edges come from adjacent lanes by SHFL.
 template <int NW, int CH>
 __device__ __forceinline__ void hsum(const uint32_t (&E)[NW], const uint32_t (&O)[NW],
                                      uint32_t (&hE)[NW], uint32_t (&hO)[NW]) {
+    uint32_t tE[NW], tO[NW];
     if constexpr (CH == 1) {
-        const uint32_t Op = __shfl_up_sync(kFull, O[NW - 1], 1);
         const uint32_t En = __shfl_down_sync(kFull, E[0], 1);
 #pragma unroll
         for (int i = 0; i < NW; ++i) {
-            const uint32_t ol = __funnelshift_l(i ? O[i - 1] : Op, O[i], 16);          // bytes -1, 1
-            const uint32_t er = __funnelshift_l(E[i], (i + 1 < NW) ? E[i + 1] : En, 16);  // bytes 2, 4
-            hE[i] = ol + 2u * E[i] + O[i];
-            hO[i] = E[i] + 2u * O[i] + er;
+            tE[i] = E[i] + O[i];                                                          // p0+p1, p2+p3
+            tO[i] = __funnelshift_l(E[i], (i + 1 < NW) ? E[i + 1] : En, 16) + O[i];      // p1+p2, p3+p4
+        }
+        const uint32_t tOp = __shfl_up_sync(kFull, tO[NW - 1], 1);
+#pragma unroll
+        for (int i = 0; i < NW; ++i) {
+            hE[i] = __funnelshift_l(i ? tO[i - 1] : tOp, tO[i], 16) + tE[i];              // t[-1]+t[0], t[1]+t[2]
+            hO[i] = tE[i] + tO[i];                                                        // t[0]+t[1], t[2]+t[3]
         }
     } else {
-        const uint32_t Op = __shfl_up_sync(kFull, O[NW - 1], 1);
-        const uint32_t Ep = __shfl_up_sync(kFull, E[NW - 1], 1);
         const uint32_t On = __shfl_down_sync(kFull, O[0], 1);
         const uint32_t En = __shfl_down_sync(kFull, E[0], 1);
 #pragma unroll
         for (int i = 0; i < NW; ++i) {
-            const uint32_t op = i ? O[i - 1] : Op;                 // bytes -3, -1
-            const uint32_t ep = i ? E[i - 1] : Ep;
-            const uint32_t on = (i + 1 < NW) ? O[i + 1] : On;
-            const uint32_t en = (i + 1 < NW) ? E[i + 1] : En;     // bytes 4, 6
-            hE[i] = op + 2u * E[i] + __funnelshift_l(O[i], on, 16);   // bytes 3, 5
-            hO[i] = __funnelshift_l(ep, E[i], 16) + 2u * O[i] + en;   // bytes -2, 0
+            tE[i] = __funnelshift_l(O[i], (i + 1 < NW) ? O[i + 1] : On, 16) + E[i];      // p0+p3, p2+p5
+            tO[i] = ((i + 1 < NW) ? E[i + 1] : En) + O[i];                                // p1+p4, p3+p6
+        }
+        const uint32_t tOp = __shfl_up_sync(kFull, tO[NW - 1], 1);
+        const uint32_t tEp = __shfl_up_sync(kFull, tE[NW - 1], 1);
+#pragma unroll
+        for (int i = 0; i < NW; ++i) {
+            hE[i] = (i ? tO[i - 1] : tOp) + tE[i];                                        // t[-3]+t[0], t[-1]+t[2]
+            hO[i] = __funnelshift_l(i ? tE[i - 1] : tEp, tE[i], 16) + tO[i];              // t[-2]+t[1], t[0]+t[3]
         }
     }
 }
 
+// Per-stage sliding window of separable partial sums.  Three register slots per
+// (stage, word, parity) rotate roles every input row:
+//   hp = h(r-1)            sp = h(r-2)+h(r-1)            tmp = scratch for h(r)
+// In phase P the roles sit in slots (3-P)%3, +1, +2; after hp += h the slot that held
+// hp holds the new sp, tmp holds the new hp, and the old sp slot is free — so with the
+// row loop unrolled by three no register-to-register moves are needed at all.
 template <int K, int NW>
 struct PipeState {
-    uint32_t hE[K][NW], hO[K][NW];  // h of the previous input row, per stage
-    uint32_t sE[K][NW], sO[K][NW];  // h(r-2)+h(r-1), per stage
+    uint32_t E[3][K][NW], O[3][K][NW];
 };
 
-// One warp's stream.  EDGE: re-impose the ZERO boundary after every stage.
-template <int K, int NW, int CH, bool EDGE, bool CHECK>
-__device__ __forceinline__ void stream_band(const PassParams &p, const int band, const int chunk,
+// One warp's stream.
+//   GENERAL = false: interior fast path — no boundary masks, no partial strips, no halo
+//                    pushes; the only per-row predicate is "does this row get stored".
+//   GENERAL = true : warps that touch an image edge (ZERO boundary re-imposed after every
+//                    stage), own a partial last strip, or hold part of the halo ring.
+template <int K, int NW, int CH, bool GENERAL, bool CHECK, class Feed>
+__device__ __forceinline__ void stream_band(const PassParams &p, Feed &feed, const int band, const int chunk,
                                             const int lane, const bool do_push,
                                             const bool top, const bool bot, const bool west, const bool east) {
     constexpr int SB = NW * 4;
@@ -163,10 +186,14 @@ __device__ __forceinline__ void stream_band(const PassParams &p, const int band,
     const int band_lo = band * p.vw, band_hi = min(band_lo + p.vw, p.bw);
     const bool st_any = xs >= band_lo && xs < band_hi;
     const int st_bytes = st_any ? min(SB, p.bw - xs) : 0;  // SB = full strip
+    // Row r is stored (as output row r-K) iff 0 <= r - first_r < nstore; lanes that store
+    // nothing get nstore = 0, so one unsigned compare per row decides everything.
+    const int first_r = out_r0 + K;
+    const unsigned nstore = st_any ? (unsigned)(out_r1 - out_r0) : 0u;
 
-    // Column masks (EDGE): lanes of bytes outside the image become 0.
+    // Column masks (GENERAL): lanes of bytes outside the image become 0.
     uint32_t mE[NW], mO[NW];
-    if constexpr (EDGE) {
+    if constexpr (GENERAL) {
 #pragma unroll
         for (int i = 0; i < NW; ++i) {
             uint32_t me = 0, mo = 0;
@@ -183,9 +210,11 @@ __device__ __forceinline__ void stream_band(const PassParams &p, const int band,
 
     PipeState<K, NW> st;
 #pragma unroll
-    for (int j = 0; j < K; ++j)
+    for (int q = 0; q < 3; ++q)
 #pragma unroll
-        for (int i = 0; i < NW; ++i) st.hE[j][i] = st.hO[j][i] = st.sE[j][i] = st.sO[j][i] = 0;
+        for (int j = 0; j < K; ++j)
+#pragma unroll
+            for (int i = 0; i < NW; ++i) st.E[q][j][i] = st.O[q][j][i] = 0;
 
     uint32_t chg = 0;
     uint32_t pE[NW], pO[NW];  // CHECK: last stage's input lanes seen one step earlier
@@ -194,32 +223,19 @@ __device__ __forceinline__ void stream_band(const PassParams &p, const int band,
         for (int i = 0; i < NW; ++i) pE[i] = pO[i] = 0;
     }
 
-    const uint8_t *src = p.src + (long long)in_r0 * p.pitch + xs;
-    long long doff = (long long)(in_r0 - K) * p.pitch + xs;  // output row r-K for input row r
+    // Output pointer of the row that input row r produces (row r-K); advanced by the loop.
+    uint8_t *dptr = p.dst + (long long)(in_r0 - K) * p.pitch + xs;
 
-    // Two rows of register prefetch.
-    uint32_t w0[NW], w1[NW];
-    load_strip<NW>(src, w0);
-    if (in_r0 + 1 < in_r1) load_strip<NW>(src + p.pitch, w1);
-    else {
-#pragma unroll
-        for (int i = 0; i < NW; ++i) w1[i] = 0;
-    }
-
-    for (int r = in_r0; r < in_r1; ++r, doff += p.pitch) {
-        uint32_t w[NW];
-#pragma unroll
-        for (int i = 0; i < NW; ++i) { w[i] = w0[i]; w0[i] = w1[i]; }
-        if (r + 2 < in_r1) load_strip<NW>(src + 2 * p.pitch, w1);
-        src += p.pitch;
-
+    // One input row through all K stages.  PH = r mod 3 relative to the first row.
+    auto row = [&](auto phase_c, const uint32_t (&w)[NW], const int r, uint8_t *const dst) {
+        constexpr int PH = decltype(phase_c)::value;
+        constexpr int HP = (3 - PH) % 3, SP = (HP + 1) % 3, TM = (HP + 2) % 3;
         uint32_t E[NW], O[NW];
 #pragma unroll
         for (int i = 0; i < NW; ++i) {
             E[i] = w[i] & 0x00ff00ffu;
-            O[i] = (w[i] >> 8) & 0x00ff00ffu;
+            O[i] = __byte_perm(w[i], 0u, 0x4341);
         }
-        uint32_t vE[NW], vO[NW];
         uint32_t cE[NW], cO[NW];  // CHECK: row r-K of iteration K-1 (input of the last stage)
 #pragma unroll
         for (int j = 0; j < K; ++j) {
@@ -229,29 +245,27 @@ __device__ __forceinline__ void stream_band(const PassParams &p, const int band,
                     for (int i = 0; i < NW; ++i) { cE[i] = pE[i]; cO[i] = pO[i]; pE[i] = E[i]; pO[i] = O[i]; }
                 }
             }
-            uint32_t hE[NW], hO[NW];
-            hsum<NW, CH>(E, O, hE, hO);
+            hsum<NW, CH>(E, O, st.E[TM][j], st.O[TM][j]);
 #pragma unroll
             for (int i = 0; i < NW; ++i) {
-                const uint32_t se = st.hE[j][i] + hE[i], so = st.hO[j][i] + hO[i];
-                vE[i] = st.sE[j][i] + se;
-                vO[i] = st.sO[j][i] + so;
-                st.hE[j][i] = hE[i]; st.hO[j][i] = hO[i];
-                st.sE[j][i] = se;    st.sO[j][i] = so;
+                st.E[HP][j][i] += st.E[TM][j][i];   // h(r-1) + h(r): next row's sp
+                st.O[HP][j][i] += st.O[TM][j][i];
+                E[i] = st.E[SP][j][i] + st.E[HP][j][i];  // v of row r-j-1 (16-bit lanes)
+                O[i] = st.O[SP][j][i] + st.O[HP][j][i];
             }
             if (j + 1 < K) {
                 // stage j output = row r-j-1 after iteration j+1, kept as lanes for stage j+1
 #pragma unroll
                 for (int i = 0; i < NW; ++i) {
                     if ((j & 1) == 0) {  // inputs had scale 1 -> lanes become 16*out
-                        E[i] = vE[i] & 0x0ff00ff0u;
-                        O[i] = vO[i] & 0x0ff00ff0u;
+                        E[i] &= 0x0ff00ff0u;
+                        O[i] &= 0x0ff00ff0u;
                     } else {             // inputs had scale 16 -> the high byte of a lane is out
-                        E[i] = __byte_perm(vE[i], 0u, 0x4341);
-                        O[i] = __byte_perm(vO[i], 0u, 0x4341);
+                        E[i] = __byte_perm(E[i], 0u, 0x4341);
+                        O[i] = __byte_perm(O[i], 0u, 0x4341);
                     }
                 }
-                if constexpr (EDGE) {
+                if constexpr (GENERAL) {
                     const int srow = r - j - 1;
                     const bool rok = (srow >= 0 || !p.zero_n) && (srow < p.rows || !p.zero_s);
 #pragma unroll
@@ -264,16 +278,14 @@ __device__ __forceinline__ void stream_band(const PassParams &p, const int band,
         }
 
         // Final stage output: row r-K, packed back to bytes.
-        const int orow = r - K;
-        if (orow >= out_r0 && st_any) {
+        if ((unsigned)(r - first_r) < nstore) {
             uint32_t o[NW];
 #pragma unroll
             for (int i = 0; i < NW; ++i) {
-                if ((K - 1) & 1) o[i] = __byte_perm(vE[i], vO[i], 0x7351);
-                else o[i] = __byte_perm(vE[i] >> 4, vO[i] >> 4, 0x6240);
+                if ((K - 1) & 1) o[i] = __byte_perm(E[i], O[i], 0x7351);
+                else o[i] = __byte_perm(E[i] >> 4, O[i] >> 4, 0x6240);
             }
-            uint8_t *dst = p.dst + doff;
-            if (st_bytes == SB) store_strip<NW>(dst, o);
+            if (!GENERAL || st_bytes == SB) store_strip<NW>(dst, o);
             else store_strip_partial<NW>(dst, o, st_bytes);
 
             if constexpr (CHECK) {
@@ -289,26 +301,42 @@ __device__ __forceinline__ void stream_band(const PassParams &p, const int band,
                 }
             }
 
-            if (do_push) {
-                const HaloParams &h = p.halo;
-                const int F = h.depth;
-                const long long up = (long long)p.rows * p.pitch, dn = -up;
-                const bool rt = orow < F, rb = orow >= p.rows - F;
-                const bool cw = xs < F * CH, ce = xs + SB > p.bw - F * CH;
-                if (top && rt && h.peer_dst[B2C_N]) store_strip<NW>(h.peer_dst[B2C_N] + doff + up, o);
-                if (bot && rb && h.peer_dst[B2C_S]) store_strip<NW>(h.peer_dst[B2C_S] + doff + dn, o);
-                if (west && cw) {
-                    if (h.peer_dst[B2C_W]) store_strip<NW>(h.peer_dst[B2C_W] + doff + p.bw, o);
-                    if (top && rt && h.peer_dst[B2C_NW]) store_strip<NW>(h.peer_dst[B2C_NW] + doff + up + p.bw, o);
-                    if (bot && rb && h.peer_dst[B2C_SW]) store_strip<NW>(h.peer_dst[B2C_SW] + doff + dn + p.bw, o);
-                }
-                if (east && ce) {
-                    if (h.peer_dst[B2C_E]) store_strip<NW>(h.peer_dst[B2C_E] + doff - p.bw, o);
-                    if (top && rt && h.peer_dst[B2C_NE]) store_strip<NW>(h.peer_dst[B2C_NE] + doff + up - p.bw, o);
-                    if (bot && rb && h.peer_dst[B2C_SE]) store_strip<NW>(h.peer_dst[B2C_SE] + doff + dn - p.bw, o);
+            if constexpr (GENERAL) {
+                if (do_push) {
+                    const HaloParams &h = p.halo;
+                    const int F = h.depth, orow = r - K;
+                    const long long doff = dst - p.dst;
+                    const long long up = (long long)p.rows * p.pitch, dn = -up;
+                    const bool rt = orow < F, rb = orow >= p.rows - F;
+                    const bool cw = xs < F * CH, ce = xs + SB > p.bw - F * CH;
+                    if (top && rt && h.peer_dst[B2C_N]) store_strip<NW>(h.peer_dst[B2C_N] + doff + up, o);
+                    if (bot && rb && h.peer_dst[B2C_S]) store_strip<NW>(h.peer_dst[B2C_S] + doff + dn, o);
+                    if (west && cw) {
+                        if (h.peer_dst[B2C_W]) store_strip<NW>(h.peer_dst[B2C_W] + doff + p.bw, o);
+                        if (top && rt && h.peer_dst[B2C_NW]) store_strip<NW>(h.peer_dst[B2C_NW] + doff + up + p.bw, o);
+                        if (bot && rb && h.peer_dst[B2C_SW]) store_strip<NW>(h.peer_dst[B2C_SW] + doff + dn + p.bw, o);
+                    }
+                    if (east && ce) {
+                        if (h.peer_dst[B2C_E]) store_strip<NW>(h.peer_dst[B2C_E] + doff - p.bw, o);
+                        if (top && rt && h.peer_dst[B2C_NE]) store_strip<NW>(h.peer_dst[B2C_NE] + doff + up - p.bw, o);
+                        if (bot && rb && h.peer_dst[B2C_SE]) store_strip<NW>(h.peer_dst[B2C_SE] + doff + dn - p.bw, o);
+                    }
                 }
             }
         }
+    };
+
+    // Rows arrive three at a time from the feed (register-prefetched LDGs or a TMA-filled
+    // shared-memory ring); rows past in_r1 carry junk whose outputs are never stored.
+    feed.start(x0, in_r0, in_r1);
+    const long long pitch = p.pitch;
+    for (int r = in_r0; r < in_r1; r += 3) {
+        uint32_t w0[NW], w1[NW], w2[NW];
+        feed.fetch3(r, w0, w1, w2);
+        row(std::integral_constant<int, 0>{}, w0, r, dptr);
+        row(std::integral_constant<int, 1>{}, w1, r + 1, dptr + pitch);
+        row(std::integral_constant<int, 2>{}, w2, r + 2, dptr + 2 * pitch);
+        dptr += 3 * pitch;
     }
     if constexpr (CHECK) {
         chg = __reduce_or_sync(kFull, chg);
@@ -339,13 +367,50 @@ __device__ __forceinline__ void map_work(int id, int NB, int NC, int nbw, int nb
     band = nbw + id % inner;
 }
 
-template <int K, int NW, int CH, bool CHECK>
-__global__ void __launch_bounds__(kWarpsPerCta * 32)
-stream_kernel(const PassParams p) {
-    const int lane = threadIdx.x & 31;
-    const int wid = blockIdx.x * kWarpsPerCta + (threadIdx.x >> 5);
-    if (wid >= p.nbands * p.nchunks) return;
-    if (p.converged && *p.converged) return;  // fixed point already reached: nothing changes any more
+// Feed #1: per-lane 16/8/4-byte LDGs, three rows held in registers ahead of use, plus an
+// optional L2 prefetch further ahead.
+template <int NW>
+struct LdgFeed {
+    const PassParams &p;
+    const int lane;
+    const uint8_t *src;
+    int in_r1;
+    uint32_t a[NW], b[NW], c[NW];
+    __device__ __forceinline__ LdgFeed(const PassParams &p_, int lane_) : p(p_), lane(lane_) {}
+    __device__ __forceinline__ void start(int x0, int in_r0, int in_r1_) {
+        in_r1 = in_r1_;
+        src = p.src + (long long)in_r0 * p.pitch + x0 + lane * NW * 4;
+#pragma unroll
+        for (int i = 0; i < NW; ++i) a[i] = b[i] = c[i] = 0;
+        // rows up to in_r1+4 are read without a guard: the frame has kFrameRows >= 8+4 rows
+        load_strip<NW>(src, a);
+        load_strip<NW>(src + p.pitch, b);
+        load_strip<NW>(src + 2 * p.pitch, c);
+        for (int q = 3; q < p.pf_rows && in_r0 + q < in_r1; ++q)
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(src + (long long)q * p.pitch));
+    }
+    __device__ __forceinline__ void fetch3(int r, uint32_t (&w0)[NW], uint32_t (&w1)[NW], uint32_t (&w2)[NW]) {
+#pragma unroll
+        for (int i = 0; i < NW; ++i) { w0[i] = a[i]; w1[i] = b[i]; w2[i] = c[i]; }
+        src += 3 * p.pitch;
+        if (r + 3 < in_r1) {   // one guard per group keeps the reads inside the frame
+            load_strip<NW>(src, a);
+            load_strip<NW>(src + p.pitch, b);
+            load_strip<NW>(src + 2 * p.pitch, c);
+        }
+        if (p.pf_rows > 0) {
+#pragma unroll
+            for (int q = 0; q < 3; ++q)
+                if (r + p.pf_rows + q < in_r1)
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(src + (long long)(p.pf_rows - 3 + q) * p.pitch));
+        }
+    }
+};
+
+// Whole per-warp program shared by the LDG and TMA kernels: pick the work item, wait for the
+// neighbours' epoch if this warp touches a halo frame, stream the band, publish our epoch.
+template <int K, int NW, int CH, bool CHECK, class MakeFeed>
+__device__ __forceinline__ void stream_warp(const PassParams &p, const int wid, const int lane, MakeFeed make_feed) {
     int band, chunk;
     map_work(wid, p.nbands, p.nchunks, p.halo.nbw, p.halo.nbe, band, chunk);
 
@@ -355,6 +420,7 @@ stream_kernel(const PassParams p) {
     const int in_r1 = min((chunk + 1) * p.chunk_rows, p.rows) + K;
     const bool edge = (p.zero_w && x0 < 0) || (p.zero_e && x0 + 32 * SB > p.bw) ||
                       (p.zero_n && in_r0 < 0) || (p.zero_s && in_r1 > p.rows);
+    const bool partial = (p.bw % SB) != 0 && (band + 1) * p.vw >= p.bw;  // owns the cut last strip
 
     bool top = false, bot = false, west = false, east = false;
     const HaloParams &h = p.halo;
@@ -384,10 +450,13 @@ stream_kernel(const PassParams p) {
     }
     const bool do_push = h.enabled && h.push && (top || bot || west || east);
 
-    if (edge) stream_band<K, NW, CH, true, CHECK>(p, band, chunk, lane, do_push, top, bot, west, east);
-    else      stream_band<K, NW, CH, false, CHECK>(p, band, chunk, lane, do_push, top, bot, west, east);
+    auto feed = make_feed();
+    if (edge || partial || do_push)
+        stream_band<K, NW, CH, true, CHECK>(p, feed, band, chunk, lane, do_push, top, bot, west, east);
+    else
+        stream_band<K, NW, CH, false, CHECK>(p, feed, band, chunk, lane, false, false, false, false, false);
 
-    if (h.enabled && h.push && (top || bot || west || east)) {
+    if (do_push) {
         // All of this warp's remote stores are issued; make them visible system-wide,
         // then count in.  The last pusher per direction publishes the epoch.
         __threadfence_system();
@@ -406,6 +475,16 @@ stream_kernel(const PassParams p) {
             }
         }
     }
+}
+
+template <int K, int NW, int CH, bool CHECK>
+__global__ void __launch_bounds__(kWarpsPerCta * 32, B2C_MIN_CTAS)
+stream_kernel(const PassParams p) {
+    const int lane = threadIdx.x & 31;
+    const int wid = blockIdx.x * kWarpsPerCta + (threadIdx.x >> 5);
+    if (wid >= p.nbands * p.nchunks) return;
+    if (p.converged && *p.converged) return;  // fixed point already reached: nothing changes any more
+    stream_warp<K, NW, CH, CHECK>(p, wid, lane, [&]() { return LdgFeed<NW>(p, lane); });
 }
 
 }  // namespace b2c

@@ -21,7 +21,6 @@ class LocalGrid:
         n = self.grid[0] * self.grid[1]
         self.devices = [torch.cuda.current_device()] * n if devices is None else list(devices)
         self.multi_device = len(set(self.devices)) == n and n > 1
-        self.tb = int(opts.get("tb", 0)) or 4
         self.engines = []
         for k in range(n):
             with torch.cuda.device(self.devices[k]):
@@ -29,6 +28,11 @@ class LocalGrid:
                                            device=self.devices[k], **opts))
         if n > 1 or opts.get("boundary") == "torus":
             Engine.connect_local(self.engines)
+        # fused iterations per pass as the engine planned them ("tb=K" in its description)
+        import re
+
+        m = re.search(r"tb=(\d+)", self.engines[0].describe())
+        self.tb = int(m.group(1)) if m else 1
 
     def close(self):
         for e in self.engines:
@@ -65,7 +69,9 @@ class LocalGrid:
             # the cross-rank OR waits on every rank's kernel: impossible to emulate on one GPU
             raise ValueError("check_every needs one GPU per rank")
         while left > 0:
-            k = min(step, left)
+            k = step
+            while k > left:  # exactly ONE pass per rank per round: k in {tb, tb/2, ..., 1}
+                k //= 2
             for r, e in enumerate(self.engines):
                 with torch.cuda.device(self.devices[r]):
                     e.run(k)

@@ -1,0 +1,69 @@
+"""Worker for test_gpu_dist.py: one rank per GPU under torch.distributed.run.
+Each rank blurs its block with the peer-memory halo engine; rank 0 checks the gathered
+image against the 1-rank CPU oracle."""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import b200conv  # noqa: E402
+from b200conv.parallel import block_of  # noqa: E402
+
+
+def main():
+    local = int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
+    rank, world = dist.get_rank(), dist.get_world_size()
+    cases = [
+        # (H, W, ch, reps, boundary, opts)
+        (256, 512, 3, 11, "zero", dict(tb=4)),
+        (256, 512, 1, 23, "torus", dict(tb=4)),
+        (240, 200, 3, 9, "zero", dict(tb=2)),          # unaligned block width -> fallback push kernel
+        (512, 1024, 3, 40, "torus", dict(tb=4, kernel="tma")),
+        (128, 256, 1, 6, "zero", dict(kernel="naive")),
+        (256, 256, 1, 400, "torus", dict(tb=4, check_every=20)),   # fused convergence across ranks
+    ]
+    ok = True
+    for (H, W, ch, reps, boundary, opts) in cases:
+        rng = np.random.default_rng(7)
+        img = rng.integers(0, 256, (H, W) if ch == 1 else (H, W, ch), dtype=np.uint8)
+        try:
+            grid = b200conv.decompose(world, H, W)
+        except b200conv.B2CError:
+            continue
+        eng = b200conv.ShardedBlur(W, H, ch, boundary=boundary, **opts)
+        r0, c0, r, c = eng.block
+        blk = torch.from_numpy(np.ascontiguousarray(img[r0:r0 + r, c0:c0 + c])).cuda()
+        eng.load(blk)
+        ms = eng.timed_run(reps)
+        iters = eng.iterations_done()
+        out = torch.empty_like(blk)
+        eng.store(out)
+        torch.cuda.synchronize()
+        parts = [torch.empty_like(out) for _ in range(world)]
+        dist.all_gather(parts, out)
+        if rank == 0:
+            full = np.empty_like(img)
+            for k, part in enumerate(parts):
+                a0, b0, a, b = block_of(k, grid, H, W)
+                full[a0:a0 + a, b0:b0 + b] = part.cpu().numpy()
+            want = b200conv.reference_oracle(img, reps, boundary)
+            good = bool((full == want).all())
+            if opts.get("check_every"):
+                good = good and iters < reps and iters % opts["check_every"] == 0
+            print(f"case {H}x{W}x{ch} reps={reps} {boundary} {opts} grid={grid} iters={iters} ms={ms:.3f} "
+                  f"{'OK' if good else 'MISMATCH'}", flush=True)
+            ok = ok and good
+        eng.close()
+    flag = torch.tensor([1 if ok else 0], device="cuda")
+    dist.broadcast(flag, 0)
+    dist.destroy_process_group()
+    sys.exit(0 if int(flag.item()) else 1)
+
+
+if __name__ == "__main__":
+    main()

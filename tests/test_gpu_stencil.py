@@ -1,0 +1,126 @@
+"""T2: every single-GPU kernel variant, byte-compared with the CPU oracle."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+import b200conv
+from b200conv import blur, reference_oracle
+
+
+def rnd(h, w, ch, seed=0):
+    return np.random.default_rng(seed).integers(0, 256, (h, w) if ch == 1 else (h, w, ch), dtype=np.uint8)
+
+
+def gpu_blur(img, reps, **kw):
+    out = blur(torch.from_numpy(img).cuda(), reps, **kw)
+    torch.cuda.synchronize()
+    return out.cpu().numpy()
+
+
+SIZES = [(1, 1), (3, 5), (17, 23), (64, 96), (130, 517), (257, 1030)]
+
+
+@pytest.mark.parametrize("boundary", ["zero", "torus"])
+@pytest.mark.parametrize("ch", [1, 3])
+@pytest.mark.parametrize("hw", SIZES)
+def test_stream_auto_matches_oracle(boundary, ch, hw):
+    img = rnd(hw[0], hw[1], ch, seed=hw[0])
+    for reps in (0, 1, 2, 3, 7, 13):
+        want = reference_oracle(img, reps, boundary)
+        got = gpu_blur(img, reps, boundary=boundary)
+        assert (got == want).all(), f"reps={reps} differs at {np.argwhere(got != want)[:4]}"
+
+
+@pytest.mark.parametrize("tb,strip", [(1, 4), (2, 4), (4, 4), (8, 4), (1, 8), (2, 8), (4, 8), (8, 8),
+                                      (1, 16), (2, 16), (4, 16)])
+@pytest.mark.parametrize("ch", [1, 3])
+@pytest.mark.parametrize("boundary", ["zero", "torus"])
+def test_stream_variants(tb, strip, ch, boundary):
+    img = rnd(150, 700 if strip == 16 else 300, ch, seed=tb * 100 + strip)
+    for reps in (tb - 1, tb, tb + 1, 2 * tb + 3):
+        if reps < 0:
+            continue
+        want = reference_oracle(img, reps, boundary)
+        got = gpu_blur(img, reps, boundary=boundary, kernel="stream", tb=tb, strip_bytes=strip)
+        assert (got == want).all(), f"tb={tb} strip={strip} reps={reps}: {np.argwhere(got != want)[:4]}"
+
+
+@pytest.mark.parametrize("tb,strip", [(1, 4), (4, 4), (8, 4), (2, 8), (8, 8), (1, 16), (2, 16), (4, 16)])
+@pytest.mark.parametrize("ch", [1, 3])
+@pytest.mark.parametrize("boundary", ["zero", "torus"])
+def test_tma_variants(tb, strip, ch, boundary):
+    """Same pipeline fed by cp.async.bulk.tensor.2d tiles + mbarriers instead of LDGs."""
+    img = rnd(150, 700 if strip == 16 else 300, ch, seed=tb * 100 + strip + 1)
+    for reps in (tb, 2 * tb + 3):
+        want = reference_oracle(img, reps, boundary)
+        got = gpu_blur(img, reps, boundary=boundary, kernel="tma", tb=tb, strip_bytes=strip)
+        assert (got == want).all(), f"tma tb={tb} strip={strip} reps={reps}: {np.argwhere(got != want)[:4]}"
+
+
+def test_tma_long_ring_wraps_many_times():
+    img = rnd(1200, 1100, 3, seed=21)  # several ring revolutions per warp
+    want = reference_oracle(img, 12, "zero")
+    for chunk_rows in (0, 400):
+        assert (gpu_blur(img, 12, kernel="tma", tb=4, chunk_rows=chunk_rows) == want).all()
+
+
+@pytest.mark.parametrize("chunk_rows", [8, 16, 37])
+def test_stream_chunking_and_graph(chunk_rows):
+    img = rnd(200, 1100, 3, seed=9)
+    want = reference_oracle(img, 40, "zero")
+    for g in (0, 1):
+        got = gpu_blur(img, 40, kernel="stream", tb=4, chunk_rows=chunk_rows, use_graph=g)
+        assert (got == want).all()
+
+
+@pytest.mark.parametrize("boundary", ["zero", "torus"])
+@pytest.mark.parametrize("ch", [1, 3])
+def test_naive_kernel(boundary, ch):
+    img = rnd(45, 77, ch, seed=4)
+    for reps in (1, 2, 5):
+        assert (gpu_blur(img, reps, boundary=boundary, kernel="naive") == reference_oracle(img, reps, boundary)).all()
+
+
+@pytest.mark.parametrize("name", ["box", "edge"])
+def test_float_filters_bit_exact(name):
+    img = rnd(40, 52, 3, seed=7)
+    for boundary in ("zero", "torus"):
+        want = reference_oracle(img, 3, boundary, filter=name)
+        assert (gpu_blur(img, 3, boundary=boundary, filter=name) == want).all()
+
+
+@pytest.mark.parametrize("ch", [1, 3])
+def test_cuda_compat_mode(ch):
+    img = rnd(33, 41, ch, seed=11)
+    for reps in (0, 1, 2, 3, 6):
+        want = reference_oracle(img, reps, "cuda-compat")
+        out, iters = blur(torch.from_numpy(img).cuda(), reps, boundary="cuda-compat", return_iterations=True)
+        assert iters == 2 * (reps // 2)
+        assert (out.cpu().numpy() == want).all()
+
+
+def test_cpu_tensor_roundtrip_and_40_reps():
+    img = rnd(252, 192, 3, seed=2)
+    t = torch.from_numpy(img).pin_memory()
+    out = blur(t, 40)
+    assert not out.is_cuda
+    assert (out.numpy() == reference_oracle(img, 40, "zero")).all()
+
+
+def test_launch_counter_moves():
+    n0 = b200conv.total_launches()
+    gpu_blur(rnd(64, 64, 1), 8, kernel="stream", tb=4, use_graph=0)
+    assert b200conv.total_launches() - n0 == 2
+
+
+def test_blur_file_program(tmp_path, monkeypatch):
+    from b200conv import blur_file
+    from b200conv.utils import read_raw, write_raw
+    monkeypatch.chdir(tmp_path)
+    img = rnd(120, 96, 3, seed=3)
+    write_raw("w.raw", img)
+    loop_ms, total_ms = blur_file("w.raw", 96, 120, "rgb", 10)
+    assert loop_ms > 0 and total_ms >= loop_ms
+    assert (read_raw("blur_w.raw", 96, 120, 3) == reference_oracle(img, 10, "zero")).all()
