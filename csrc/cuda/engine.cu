@@ -234,11 +234,17 @@ std::vector<Pass> make_passes(const b2c_engine *e, int reps) {
 
 int enqueue_pass(b2c_engine *e, const Pass &ps, cudaStream_t s) {
     if (e->kernel == B2C_KERNEL_NAIVE) {
+        if (e->any_nb) {  // the naive kernel reads the frame without looking at the flags
+            unsigned mask = 0;
+            for (int d = 0; d < 8; ++d) mask |= (e->nb[d] >= 0 ? 1u : 0u) << d;
+            CK(launch_halo_wait(e->pad + kPadFlags, mask, e->epoch, s));
+            e->launches++;
+        }
         CK(launch_naive(e->base[e->cur], e->base[e->cur ^ 1], e->pitch, e->R, e->bw, e->CH, e->nw, s));
         e->launches++;
         if (e->any_nb) {
             PushParams q;
-            fill_push_params(e, e->cur ^ 1, true, q);
+            fill_push_params(e, e->cur ^ 1, false, q);
             CK(launch_halo_push(q, s));
             e->launches++;
         }

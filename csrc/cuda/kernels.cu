@@ -208,6 +208,26 @@ cudaError_t launch_halo_push(const PushParams &q, cudaStream_t s) {
     return cudaGetLastError();
 }
 
+// Blocks the stream until every neighbour has published `epoch` (used in front of kernels
+// that do not wait by themselves: the byte-per-thread naive kernel).
+__global__ void halo_wait_kernel(const uint32_t *flags, unsigned mask, uint32_t epoch) {
+    const int d = threadIdx.x;
+    if (d >= 8 || !((mask >> d) & 1u)) return;
+    const long long t0 = clock64();
+    while ((int)(ld_acquire_sys(flags + d * 32) - epoch) < 0) {
+        if (clock64() - t0 > (20ll << 30)) {
+            printf("b200conv: halo wait timeout dir=%d want=%u\n", d, epoch);
+            __trap();
+        }
+    }
+}
+
+cudaError_t launch_halo_wait(const uint32_t *flags, unsigned mask, uint32_t epoch, cudaStream_t s) {
+    halo_wait_kernel<<<1, 32, 0, s>>>(flags, mask, epoch);
+    count_launch(1);
+    return cudaGetLastError();
+}
+
 // ------------------------------------------------------------------- misc
 
 __global__ void set_u32_kernel(unsigned int *p, unsigned int v) { *p = v; }

@@ -48,6 +48,7 @@ cudaError_t launch_naive(const uint8_t *src, uint8_t *dst, long long pitch, int 
                          const NaiveWeights &w, cudaStream_t s);
 cudaError_t launch_compat(const uint8_t *src, uint8_t *dst, int W, int H, int ch, cudaStream_t s);
 cudaError_t launch_halo_push(const PushParams &q, cudaStream_t s);
+cudaError_t launch_halo_wait(const uint32_t *flags, unsigned mask, uint32_t epoch, cudaStream_t s);
 cudaError_t launch_converge(const ConvergeParams &c, cudaStream_t s);
 cudaError_t launch_set_u32(unsigned int *p, unsigned int v, cudaStream_t s);
 
