@@ -11,6 +11,7 @@
 
 #include <algorithm>
 #include <map>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -738,3 +739,137 @@ int b2c_stencil_step_device(const uint8_t *src, uint8_t *dst, int64_t pitch, int
 int64_t b2c_total_launches(void) { return total_launches(); }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------
+// Allocation-free blur (b2c_blur_device_noalloc).  No counterpart in the reference.
+//
+// b2c_blur_device needs two framed ping-pong buffers plus a flag pad and gets them from
+// cudaMalloc on every call.  Some users of this library are not allowed to do that: a
+// filter plugged into a host application that hands out all device memory up front and
+// forbids further allocation; a per-frame / real-time loop where cudaMalloc and cudaFree
+// stall the whole device for an unbounded time; a process that runs under a fixed device
+// memory budget and must not fail half-way through because an allocation was refused.
+// For them the same work runs out of a fixed scratch area that is part of the library
+// image itself: the array below.  Every GPU that loads the library carries these 32 MiB
+// until the process exits, whether or not the function is ever called.
+//
+// The scratch is shared by all calls and keeps whatever the previous call left in it, so
+// each call first clears the part it is going to use (halo frames and flag words must
+// start at zero).  Two calls whose GPU work overlaps — different streams, or different
+// host threads on different streams — corrupt each other; calls on one stream are safe.
+// ---------------------------------------------------------------------------------------
+#define B2C_NOALLOC_SCRATCH_BYTES (32ll << 20)
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[B2C_NOALLOC_SCRATCH_BYTES];
+
+namespace {
+
+// In host code `g_noalloc_scratch` is only a stand-in for the device symbol; the usable device
+// address comes from cudaGetSymbolAddress, looked up once per device with that device current.
+int noalloc_scratch_base(int dev, uint8_t **out) {
+    static uint8_t *addr[64];
+    static bool known[64];
+    static std::mutex mu;
+    if (dev < 0 || dev >= 64) {
+        set_error("blur_device_noalloc: device index %d out of range", dev);
+        return B2C_EINVAL;
+    }
+    std::lock_guard<std::mutex> lock(mu);
+    if (!known[dev]) {
+        void *p = nullptr;
+        CK(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+        addr[dev] = static_cast<uint8_t *>(p);
+        known[dev] = true;
+    }
+    *out = addr[dev];
+    return B2C_OK;
+}
+
+}  // namespace
+
+extern "C" int b2c_blur_device_noalloc(const uint8_t *d_in, int64_t in_pitch, uint8_t *d_out, int64_t out_pitch,
+                                       int W, int H, int CH, int reps, int boundary, void *stream) {
+    if (!d_in || !d_out || W <= 0 || H <= 0 || (CH != 1 && CH != 3) || reps < 0 ||
+        (boundary != B2C_ZERO && boundary != B2C_TORUS)) {
+        set_error("blur_device_noalloc: bad arguments (boundary must be zero or torus)");
+        return B2C_EINVAL;
+    }
+    int dev = 0;
+    CK(cudaGetDevice(&dev));
+    cudaStream_t s = (cudaStream_t)stream;
+
+    // A throw-away engine description on the host stack: same planner and pass scheduler as
+    // b2c_engine_create/run, but its buffers are carved out of the static scratch.
+    b2c_engine e;
+    e.device = dev; e.W = W; e.H = H; e.CH = CH; e.P = 1; e.Q = 1; e.rank = 0;
+    b2c_default_opts(&e.opts);
+    e.opts.boundary = boundary;
+    e.opts.use_graph = 0;
+    e.R = H; e.C = W; e.row0 = 0; e.col0 = 0;
+    if ((long long)W * CH > (1ll << 30)) {
+        set_error("blur_device_noalloc: row too wide");
+        return B2C_ETOOBIG;
+    }
+    e.bw = W * CH;
+    b2c_neighbours(0, 1, 1, boundary, e.nb);
+    e.any_nb = boundary == B2C_TORUS;
+    memset(e.peer_base, 0, sizeof e.peer_base);
+    memset(e.peer_pad, 0, sizeof e.peer_pad);
+    memset(e.rank_pad, 0, sizeof e.rank_pad);
+    const FilterDef &f = filter_def(B2C_GAUSSIAN);
+    for (int i = 0; i < 3; ++i)
+        for (int j = 0; j < 3; ++j) {
+            e.nw.iw[i][j] = f.w[i][j];
+            e.nw.fw[i][j] = (float)(f.w[i][j] / (double)f.den);
+        }
+    e.nw.integer16 = 1;
+    CK(cudaDeviceGetAttribute(&e.sm_count, cudaDevAttrMultiProcessorCount, dev));
+    choose_plan(&e);
+
+    e.pitch = round_up(kLeftPad + (long long)e.bw + 32 + 16, 128);
+    e.alloc_bytes = round_up(e.pitch * (e.R + 2 * kFrameRows) + 1024, 256);
+    const long long pad_bytes = kPadWords * (long long)sizeof(uint32_t);
+    const long long need = 2 * e.alloc_bytes + pad_bytes;
+    if (need > B2C_NOALLOC_SCRATCH_BYTES) {
+        set_error("blur_device_noalloc: a %dx%dx%d image needs %lld bytes of scratch but the built-in scratch is "
+                  "%lld bytes (fits up to about 1920x2520 rgb); use b2c_blur_device or an engine instead",
+                  W, H, CH, need, (long long)B2C_NOALLOC_SCRATCH_BYTES);
+        return B2C_ETOOBIG;
+    }
+    uint8_t *scratch = nullptr;
+    int rc = noalloc_scratch_base(dev, &scratch);
+    if (rc != B2C_OK) return rc;
+    e.alloc[0] = scratch;
+    e.alloc[1] = scratch + e.alloc_bytes;
+    e.pad = reinterpret_cast<uint32_t *>(scratch + 2 * e.alloc_bytes);
+    for (int i = 0; i < 2; ++i) e.base[i] = e.alloc[i] + (long long)kFrameRows * e.pitch + kLeftPad;
+
+    // The last call's image, halo frames, epoch flags and counters are still in there.
+    CK(cudaMemsetAsync(scratch, 0, (size_t)need, s));
+    if (e.any_nb) {  // torus on one GPU: the rank is its own neighbour in all eight directions
+        for (int d = 0; d < 8; ++d) {
+            e.peer_base[0][d] = e.base[0];
+            e.peer_base[1][d] = e.base[1];
+            e.peer_pad[d] = e.pad;
+        }
+        e.rank_pad[0] = e.pad;
+        e.connected = true;
+    }
+    if (in_pitch <= 0) in_pitch = e.bw;
+    if (out_pitch <= 0) out_pitch = e.bw;
+    CK(cudaMemcpy2DAsync(e.base[0], (size_t)e.pitch, d_in, (size_t)in_pitch, (size_t)e.bw, (size_t)e.R,
+                         cudaMemcpyDeviceToDevice, s));
+    if (e.any_nb) {
+        PushParams q;
+        fill_push_params(&e, e.cur, false, q);
+        CK(launch_halo_push(q, s));
+        e.epoch++;
+    }
+    for (const Pass &ps : make_passes(&e, reps)) {
+        rc = enqueue_pass(&e, ps, s);
+        if (rc != B2C_OK) return rc;
+    }
+    CK(cudaMemcpy2DAsync(d_out, (size_t)out_pitch, e.base[e.cur], (size_t)e.pitch, (size_t)e.bw, (size_t)e.R,
+                         cudaMemcpyDeviceToDevice, s));
+    return B2C_OK;
+}

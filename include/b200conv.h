@@ -206,6 +206,32 @@ int b2c_blur_device(const uint8_t *d_in, int64_t in_pitch, uint8_t *d_out, int64
                     int width, int height, int channels, int repetitions, const b2c_opts *opts,
                     void *stream);
 
+/* Same result as b2c_blur_device (gaussian; boundary B2C_ZERO or B2C_TORUS) for callers
+ * that must not allocate device memory.  This entry point has no counterpart in the
+ * reference, whose GPU program cudaMallocs on every run.
+ *
+ * Who needs it: a filter running inside a host application that owns all device memory and
+ * forbids plugins to allocate; a per-frame or real-time loop that cannot afford the
+ * device-wide stall and unbounded latency of cudaMalloc/cudaFree; a job with a fixed device
+ * memory budget that must not fail mid-run on a refused allocation.
+ *
+ * The call performs no cudaMalloc/cudaFree and no allocating library call.  Its two work
+ * buffers and flag words live in a fixed 32 MiB scratch array that is part of the library
+ * image (every GPU that loads the library holds it until the process exits).  Limit: the
+ * padded image must fit, 2 * (round_up(W*CH + 80, 128) * (H + 24) + 1024) + 4096 <= 32 MiB,
+ * which covers images up to about 1920x2520 rgb; larger ones are rejected with
+ * B2C_ETOOBIG and a message from b2c_last_error().
+ *
+ * The first call on a device looks up the scratch array's device address (with that device
+ * current) and caches it; make that first call before starting any stream capture.
+ * The work is enqueued on `stream` and the function returns without synchronising.  All
+ * calls share the one scratch area: it is cleared at the start of each call, and calls
+ * whose GPU work overlaps in time (different streams) race with each other — keep them on
+ * one stream or serialise them yourself.  `in_pitch` / `out_pitch` <= 0 mean tight rows. */
+int b2c_blur_device_noalloc(const uint8_t *d_in, int64_t in_pitch, uint8_t *d_out, int64_t out_pitch,
+                            int width, int height, int channels, int repetitions, int boundary,
+                            void *stream);
+
 /* One plain iteration on caller-owned framed memory: `src`/`dst` point at the
  * interior origin of buffers that have at least one halo row above/below and
  * `channels` halo bytes left/right (the caller fills the halo, e.g. with NCCL
