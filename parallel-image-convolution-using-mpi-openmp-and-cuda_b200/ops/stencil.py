@@ -187,6 +187,18 @@ def stencil_step(src: torch.Tensor, dst: torch.Tensor, rows: int, row_bytes: int
                                       int(channels), FILTER[filter], _stream_ptr()), "stencil_step")
 
 
+def load_torch_ops():
+    """Load ``lib/_b200conv_torch.so`` (the thin C++ PyTorch binding) and return
+    ``torch.ops.b200conv`` — ``torch.ops.b200conv.blur(img, reps, boundary, filter, tb, kernel)``."""
+    from .._lib import PKG_DIR
+
+    so = PKG_DIR / "lib" / "_b200conv_torch.so"
+    if not so.exists():
+        raise B2CError(f"{so} is not built; run `python build.py`")
+    torch.ops.load_library(str(so))
+    return torch.ops.b200conv
+
+
 def blur_file(path: str, width: int, height: int, color: str, repetitions: int, **opts):
     """Whole-program run on one GPU: read ``path``, blur, write ``blur_<path>``.
     Returns ``(loop_ms, total_ms)``."""

@@ -124,3 +124,15 @@ def test_blur_file_program(tmp_path, monkeypatch):
     loop_ms, total_ms = blur_file("w.raw", 96, 120, "rgb", 10)
     assert loop_ms > 0 and total_ms >= loop_ms
     assert (read_raw("blur_w.raw", 96, 120, 3) == reference_oracle(img, 10, "zero")).all()
+
+
+def test_torch_ops_binding():
+    """torch.ops.b200conv.blur — the thin C++ PyTorch extension over the same core."""
+    from b200conv.ops import load_torch_ops
+
+    ops = load_torch_ops()
+    img = rnd(70, 90, 3, seed=13)
+    out = ops.blur(torch.from_numpy(img).cuda(), 6, "torus", "gaussian", 4, "auto")
+    torch.cuda.synchronize()
+    assert (out.cpu().numpy() == reference_oracle(img, 6, "torus")).all()
+    assert ops.rows_division(4, 2520, 1920) == 2
