@@ -59,6 +59,25 @@ def main():
                   f"{'OK' if good else 'MISMATCH'}", flush=True)
             ok = ok and good
         eng.close()
+    # the NCCL send/recv baseline must be exact as well (it is the comparison arm of the benches)
+    from b200conv.parallel.nccl_baseline import NcclHaloBlur
+    for boundary in ("zero", "torus"):
+        H, W, ch, reps = 96, 192, 3, 7
+        img = np.random.default_rng(9).integers(0, 256, (H, W, ch), dtype=np.uint8)
+        nb = NcclHaloBlur(W, H, ch, boundary=boundary)
+        nb.load(torch.from_numpy(np.ascontiguousarray(img[nb.r0:nb.r0 + nb.R, nb.c0:nb.c0 + nb.C])).cuda())
+        nb.run(reps)
+        out = nb.store()
+        parts = [torch.empty_like(out) for _ in range(world)]
+        dist.all_gather(parts, out)
+        if rank == 0:
+            full = np.empty_like(img)
+            for k, part in enumerate(parts):
+                a0, b0, a, b = block_of(k, nb.grid, H, W)
+                full[a0:a0 + a, b0:b0 + b] = part.cpu().numpy()
+            good = bool((full == b200conv.reference_oracle(img, reps, boundary)).all())
+            print(f"case nccl-baseline {boundary} {'OK' if good else 'MISMATCH'}", flush=True)
+            ok = ok and good
     flag = torch.tensor([1 if ok else 0], device="cuda")
     dist.broadcast(flag, 0)
     dist.destroy_process_group()
