@@ -10,6 +10,7 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <cmath>
 #include <map>
 #include <mutex>
 #include <string>
@@ -105,33 +106,64 @@ struct b2c_engine {
 
 namespace {
 
+// Window geometry of a k-stage pass for the engine's strip width.
+void band_geometry(const b2c_engine *e, int k, int *hlo, int *vw, int *nbands) {
+    // window start and band pitch: strip-aligned for per-lane LDGs, 16 B for TMA box origins
+    const int align = e->kernel == B2C_KERNEL_TMA ? 16 : e->SB;
+    *hlo = (int)round_up((long long)k * e->CH, align);
+    *vw = (int)round_down(32 * e->SB - *hlo - k * e->CH, align);
+    *nbands = (int)ceil_div(e->bw, *vw);
+}
+
+// Modelled time of one k-stage pass (microseconds, relative) for `cr` rows per warp, from
+// the constants measured on B200 (profiles/tuning.md):
+//   * one warp needs ~64 ns per stage per row (SHFL -> add -> SHFL -> add chain), so a
+//     pass cannot finish faster than waves x (cr + 2k) x k x 64 ns — what small images see;
+//   * the whole chip retires ~7 T raw byte-iterations/s with 16 B strips (a little less with
+//     narrower ones: more SHFL per byte), what large images see; several waves are fine
+//     there (the block scheduler back-fills), one exact wave is not (no back-fill).
+double plan_cost(const b2c_engine *e, int k, int cr) {
+    int hlo, vw, nb;
+    band_geometry(e, k, &hlo, &vw, &nb);
+    int occ = e->kernel == B2C_KERNEL_TMA ? stream_tma_occupancy(k, e->SB, e->CH) : stream_occupancy(k, e->SB, e->CH);
+    if (occ <= 0) occ = 4;
+    const double wave = (double)e->sm_count * occ * kWarpsPerCta;
+    const long long nc = ceil_div(e->R, cr);
+    const double warps = (double)nb * nc;
+    const double t_lat = std::ceil(warps / wave) * (cr + 2 * k) * k * 0.064;
+    const double rate = e->SB == 16 ? 7.2e6 : (e->SB == 8 ? 7.0e6 : 5.5e6);  // raw byte-iterations per us
+    const double util = std::min(1.0, warps / wave);       // a half-empty chip runs at half rate
+    const double waves_f = std::max(1.0, warps / wave);
+    // with about one wave nothing back-fills the SMs that finish early (+30 % measured)
+    const double t_thr = warps * 32.0 * e->SB * (cr + 2 * k) * k / (rate * util) * (1.0 + 0.3 / waves_f);
+    return std::max(t_lat, t_thr);
+}
+
+double best_chunk_rows(const b2c_engine *e, int k, int *out) {
+    static const int cand[] = {8, 12, 16, 24, 32, 48, 64, 96, 128, 192, 256, 384, 512};
+    double best = 1e300;
+    int best_cr = std::max(1, e->R);
+    for (int c : cand) {
+        int cr = std::max(c, std::max(2 * k, e->F));
+        cr = std::min(cr, std::max(e->R, 1));
+        const double t = plan_cost(e, k, cr);
+        if (t < best * 0.999) { best = t; best_cr = cr; }
+        if (cr >= e->R) break;
+    }
+    *out = best_cr;
+    return best;
+}
+
 BandPlan make_band_plan(const b2c_engine *e, int k) {
     if (k >= 1 && k <= 8 && e->plan_ok[k]) return e->plan_cache[k];
     BandPlan bp{};
-    const int SB = e->SB, CH = e->CH;
-    // window start and band pitch: strip-aligned for per-lane LDGs, 16 B for TMA box origins
-    const int align = e->kernel == B2C_KERNEL_TMA ? 16 : SB;
-    bp.hlo = (int)round_up((long long)k * CH, align);
-    bp.vw = (int)round_down(32 * SB - bp.hlo - k * CH, align);
-    bp.nbands = (int)ceil_div(e->bw, bp.vw);
-    // Rows per warp.  All warps cost the same, so the grid is sized to whole waves of
-    // resident warps (occupancy x SMs): a partial last wave would idle most of the chip.
+    const int CH = e->CH;
+    band_geometry(e, k, &bp.hlo, &bp.vw, &bp.nbands);
     int chunk_rows = e->opts.chunk_rows;
     if (chunk_rows <= 0) {
-        int occ = e->kernel == B2C_KERNEL_TMA ? stream_tma_occupancy(k, SB, CH) : stream_occupancy(k, SB, CH);
-        if (occ <= 0) occ = 4;
-        const long long wave = (long long)e->sm_count * occ * kWarpsPerCta;  // warps resident at once
-        // Measured on B200 (profiles/tuning.md): many short streams beat one wave of long
-        // ones — CTAs finish at different times and the block scheduler back-fills — until
-        // the 2k-row pipeline fill per chunk starts to cost.  Aim for >= 4 waves of warps
-        // with 128..256-row chunks; never below 8k rows (fill <= 25 %).
-        const int min_rows = std::max(8 * k, 32);
-        long long cr = (long long)e->R * bp.nbands / (4 * wave);
-        cr = std::max<long long>(min_rows, std::min<long long>(cr, 256));
-        if (cr > 128 && (long long)bp.nbands * ceil_div(e->R, 128) <= 8 * wave) cr = 128;
-        cr = std::max<long long>(cr, min_rows);
-        const int nc = (int)ceil_div(e->R, cr);
-        chunk_rows = (int)ceil_div(e->R, nc);
+        best_chunk_rows(e, k, &chunk_rows);
+        const int nc = (int)ceil_div(e->R, chunk_rows);
+        chunk_rows = (int)ceil_div(e->R, nc);   // even out the last chunk
     }
     chunk_rows = std::max(chunk_rows, e->F);
     chunk_rows = std::min(chunk_rows, std::max(e->R, 1));
@@ -167,10 +199,6 @@ void fill_pass_params(const b2c_engine *e, int k, bool check, int src_i, PassPar
     p.zero_s = zero && e->nb[B2C_S] < 0;
     p.zero_w = zero && e->nb[B2C_W] < 0;
     p.zero_e = zero && e->nb[B2C_E] < 0;
-    {
-        static const int pf = getenv("B200CONV_PF") ? atoi(getenv("B200CONV_PF")) : 0;
-        p.pf_rows = pf;
-    }
     p.changed = check ? e->pad + kPadChanged : nullptr;
     p.converged = e->opts.check_every > 0 ? e->pad + kPadConverged : nullptr;
     HaloParams &h = p.halo;
@@ -293,23 +321,23 @@ void choose_plan(b2c_engine *e) {
     if (e->kernel == B2C_KERNEL_NAIVE) K = 1;
     // a k-deep halo must come from the adjacent rank only
     if (e->any_nb) while (K > 1 && K > std::min(e->R, e->C)) K >>= 1;
+    e->K = K;
+    e->F = e->any_nb ? K : 1;
+    if (e->kernel == B2C_KERNEL_NAIVE) e->F = 1;
     int SB = o.strip_bytes;
     if (SB != 4 && SB != 8 && SB != 16) {
-        // widest strip that still yields enough warps to fill the machine
-        SB = 16;
-        while (SB > 4) {
-            const int nwords = SB / 4;
-            if (K * nwords <= 16) {
-                const int hlo = (int)round_up((long long)K * e->CH, SB);
-                const int vw = (int)round_down(32 * SB - hlo - K * e->CH, SB);
-                const long long warps = ceil_div(e->bw, vw) * ceil_div(e->R, std::max(16 * K, 32));
-                if (warps >= (long long)e->sm_count * 8) break;
-            }
-            SB >>= 1;
+        // strip width with the lowest modelled pass time (see plan_cost)
+        double best = 1e300;
+        SB = 4;
+        for (int sb = 16; sb >= 4; sb >>= 1) {
+            if (K * (sb / 4) > 16) continue;
+            e->SB = sb;
+            int cr = 0;
+            const double t = best_chunk_rows(e, K, &cr);
+            if (t < best * 0.97) { best = t; SB = sb; }   // prefer the wider strip on near ties
         }
     }
     while (K * (SB / 4) > 16) SB >>= 1;
-    e->K = K;
     e->SB = SB;
     e->F = e->any_nb ? K : 1;
     if (e->kernel == B2C_KERNEL_NAIVE) e->F = 1;

@@ -69,7 +69,6 @@ struct PassParams {
     int zero_n, zero_s, zero_w, zero_e;  // outside that side is outside the image (ZERO mode)
     unsigned int *changed;  // CHECK: OR-accumulated "last stage changed a byte"
     const unsigned int *converged;  // when set (non-null and non-zero) the pass is skipped
-    int pf_rows;         // rows ahead to prefetch into L2 (0 = off)
     HaloParams halo;
 };
 
@@ -330,6 +329,7 @@ __device__ __forceinline__ void stream_band(const PassParams &p, Feed &feed, con
     // shared-memory ring); rows past in_r1 carry junk whose outputs are never stored.
     feed.start(x0, in_r0, in_r1);
     const long long pitch = p.pitch;
+#pragma unroll 1
     for (int r = in_r0; r < in_r1; r += 3) {
         uint32_t w0[NW], w1[NW], w2[NW];
         feed.fetch3(r, w0, w1, w2);
@@ -367,8 +367,7 @@ __device__ __forceinline__ void map_work(int id, int NB, int NC, int nbw, int nb
     band = nbw + id % inner;
 }
 
-// Feed #1: per-lane 16/8/4-byte LDGs, three rows held in registers ahead of use, plus an
-// optional L2 prefetch further ahead.
+// Feed #1: per-lane 16/8/4-byte LDGs, three rows held in registers ahead of use.
 template <int NW>
 struct LdgFeed {
     const PassParams &p;
@@ -386,8 +385,6 @@ struct LdgFeed {
         load_strip<NW>(src, a);
         load_strip<NW>(src + p.pitch, b);
         load_strip<NW>(src + 2 * p.pitch, c);
-        for (int q = 3; q < p.pf_rows && in_r0 + q < in_r1; ++q)
-            asm volatile("prefetch.global.L2 [%0];" ::"l"(src + (long long)q * p.pitch));
     }
     __device__ __forceinline__ void fetch3(int r, uint32_t (&w0)[NW], uint32_t (&w1)[NW], uint32_t (&w2)[NW]) {
 #pragma unroll
@@ -397,12 +394,6 @@ struct LdgFeed {
             load_strip<NW>(src, a);
             load_strip<NW>(src + p.pitch, b);
             load_strip<NW>(src + 2 * p.pitch, c);
-        }
-        if (p.pf_rows > 0) {
-#pragma unroll
-            for (int q = 0; q < 3; ++q)
-                if (r + p.pf_rows + q < in_r1)
-                    asm volatile("prefetch.global.L2 [%0];" ::"l"(src + (long long)(p.pf_rows - 3 + q) * p.pitch));
         }
     }
 };

@@ -4,6 +4,7 @@ Capabilities of theopaid/Parallel-Image-Convolution-using-MPI-OPENMP-and-CUDA (i
 MPI+OpenMP and CUDA programs) on one C++/CUDA core:
 
   ``blur(img, reps, boundary=...)``        single GPU, torch tensors
+  ``BlurPipeline``                         single GPU, stream of host images, copies overlapped
   ``parallel.ShardedBlur``                 one process per GPU, peer-memory halo exchange
   ``parallel.LocalGrid``                   every rank in one process (tests, multi-GPU threads)
   ``reference_oracle`` / ``numpy_oracle``  CPU oracles
@@ -13,7 +14,7 @@ MPI+OpenMP and CUDA programs) on one C++/CUDA core:
 """
 from . import _lib
 from ._lib import B2CError
-from .ops import (Engine, blur, blur_file, clear_engine_cache, numpy_oracle, reference_oracle, sharded_oracle,
+from .ops import (BlurPipeline, Engine, blur, blur_file, clear_engine_cache, numpy_oracle, reference_oracle, sharded_oracle,
                   stencil_step)
 from .parallel import LocalGrid, ShardedBlur, block_of, decompose, neighbours, rows_division
 from . import models, ops, parallel, utils

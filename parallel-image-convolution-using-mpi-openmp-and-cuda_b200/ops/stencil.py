@@ -173,6 +173,52 @@ def blur(img: torch.Tensor, repetitions: int, boundary: str = "zero", filter: st
     return (out, iters) if return_iterations else out
 
 
+class BlurPipeline:
+    """Throughput-oriented single-GPU API for a stream of same-shaped host images.
+
+    ``depth`` engines, each with its own CUDA stream, work round-robin: while one image is
+    being blurred, the next one is copied host->device and the previous result device->host
+    (the copy engines run beside the SMs; PCIe is full duplex).  Per image the work is still
+    H2D -> ``repetitions`` iterations -> D2H; only the waiting is overlapped.
+
+        pipe = BlurPipeline(W, H, 3, repetitions=1000)
+        for src, dst in zip(pinned_inputs, pinned_outputs):
+            pipe.submit(src, dst)
+        pipe.wait()
+    """
+
+    def __init__(self, width, height, channels, repetitions, depth=2, device=None, **opts):
+        _require_cuda()
+        self.repetitions = int(repetitions)
+        self.device = torch.cuda.current_device() if device is None else int(device)
+        with torch.cuda.device(self.device):
+            self.engines = [Engine(width, height, channels, device=self.device, **opts) for _ in range(depth)]
+            self.streams = [torch.cuda.Stream(device=self.device) for _ in range(depth)]
+        self._next = 0
+
+    def submit(self, src: torch.Tensor, dst: torch.Tensor):
+        """Enqueue one image (pinned CPU or CUDA tensors); returns immediately."""
+        i = self._next
+        self._next = (i + 1) % len(self.engines)
+        eng, st = self.engines[i], self.streams[i]
+        with torch.cuda.device(self.device):
+            eng.load(src, stream=st)
+            eng.exchange(stream=st)
+            eng.run(self.repetitions, stream=st)
+            if int(eng.opts.check_every):
+                eng.iterations_done()
+            eng.store(dst, stream=st)
+
+    def wait(self):
+        for st in self.streams:
+            st.synchronize()
+
+    def close(self):
+        self.wait()
+        for e in self.engines:
+            e.close()
+
+
 def stencil_step(src: torch.Tensor, dst: torch.Tensor, rows: int, row_bytes: int, channels: int,
                  filter: str = "gaussian"):
     """One plain iteration on caller-framed CUDA buffers (see ``b2c_stencil_step_device``).

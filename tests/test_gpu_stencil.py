@@ -136,3 +136,19 @@ def test_torch_ops_binding():
     torch.cuda.synchronize()
     assert (out.cpu().numpy() == reference_oracle(img, 6, "torus")).all()
     assert ops.rows_division(4, 2520, 1920) == 2
+
+
+def test_blur_pipeline_overlapped_steps():
+    """BlurPipeline: several host images in flight on two engines/streams, each result exact."""
+    from b200conv import BlurPipeline
+
+    imgs = [rnd(200, 300, 3, seed=30 + i) for i in range(5)]
+    srcs = [torch.from_numpy(x).pin_memory() for x in imgs]
+    dsts = [torch.empty_like(s).pin_memory() for s in srcs]
+    pipe = BlurPipeline(300, 200, 3, repetitions=12, depth=2)
+    for s, d in zip(srcs, dsts):
+        pipe.submit(s, d)
+    pipe.wait()
+    pipe.close()
+    for x, d in zip(imgs, dsts):
+        assert (d.numpy() == reference_oracle(x, 12, "zero")).all()
