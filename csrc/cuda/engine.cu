@@ -8,6 +8,7 @@
 // straight into the frame over NVLink from inside the stencil kernel; the host
 // only enqueues one kernel per K fused iterations (optionally as a CUDA graph).
 #include <cuda_runtime.h>
+#include <nvtx3/nvToolsExt.h>
 
 #include <algorithm>
 #include <cmath>
@@ -33,6 +34,12 @@
 using namespace b2c;
 
 namespace {
+
+// NVTX range for Nsight timelines (tracing hook); a no-op without a profiler attached.
+struct NvtxRange {
+    explicit NvtxRange(const char *name) { nvtxRangePushA(name); }
+    ~NvtxRange() { nvtxRangePop(); }
+};
 
 // Flag pad layout, in 32-bit words.  Every flag/counter sits on its own 128 B line.
 constexpr int kPadFlags = 0;          // 8 x 32
@@ -564,6 +571,7 @@ int b2c_engine_connect_local(b2c_engine **engines, int n) {
 
 static int copy_block(b2c_engine *e, void *user, long long upitch, cudaMemcpyKind kind, bool to_engine, void *stream) {
     if (!e || !user) return B2C_EINVAL;
+    NvtxRange nvtx(to_engine ? "b2c_engine_load" : "b2c_engine_store");
     CK(cudaSetDevice(e->device));
     cudaStream_t s = (cudaStream_t)stream;
     if (e->opts.boundary == B2C_CUDA_COMPAT) {
@@ -601,6 +609,7 @@ int b2c_engine_store_device(b2c_engine *e, uint8_t *dev, int64_t pitch, void *st
 
 int b2c_engine_exchange(b2c_engine *e, void *stream) {
     if (!e) return B2C_EINVAL;
+    NvtxRange nvtx("b2c_engine_exchange");
     if (!e->any_nb) return B2C_OK;
     if (!e->connected) {
         set_error("engine_exchange: peers are not connected (import/connect_local first)");
@@ -617,6 +626,7 @@ int b2c_engine_exchange(b2c_engine *e, void *stream) {
 
 int b2c_engine_run(b2c_engine *e, int reps, void *stream) {
     if (!e || reps < 0) return B2C_EINVAL;
+    NvtxRange nvtx("b2c_engine_run");
     CK(cudaSetDevice(e->device));
     cudaStream_t s = (cudaStream_t)stream;
     if (e->opts.boundary == B2C_CUDA_COMPAT) {

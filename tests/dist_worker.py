@@ -26,6 +26,8 @@ def main():
         (512, 1024, 3, 40, "torus", dict(tb=4, kernel="tma")),
         (128, 256, 1, 6, "zero", dict(kernel="naive")),
         (256, 256, 1, 400, "torus", dict(tb=4, check_every=20)),   # fused convergence across ranks
+        (128, 512, 3, 1000, "torus", dict(tb=4, delay=20000)),      # 250 epochs with skewed ranks
+        (128, 512, 3, 501, "zero", dict(tb=2, delay=50000)),
     ]
     ok = True
     for (H, W, ch, reps, boundary, opts) in cases:
@@ -35,7 +37,12 @@ def main():
             grid = b200conv.decompose(world, H, W)
         except b200conv.B2CError:
             continue
+        delay = opts.pop("delay", 0)
         eng = b200conv.ShardedBlur(W, H, ch, boundary=boundary, **opts)
+        if delay:
+            # T3 stress: skew the ranks against each other before every flag wait so a
+            # slot-reuse race (a frame overwritten while its owner still reads it) would corrupt bytes
+            eng.engine.set_delay(delay * (1 + (rank * 7) % 5))
         r0, c0, r, c = eng.block
         blk = torch.from_numpy(np.ascontiguousarray(img[r0:r0 + r, c0:c0 + c])).cuda()
         eng.load(blk)
