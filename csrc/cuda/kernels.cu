@@ -30,9 +30,23 @@ static cudaError_t stream_op_t(int op, const PassParams *p, bool check, cudaStre
     if (op == 1) return cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, fn, kWarpsPerCta * 32, 0);
     const int warps = p->nbands * p->nchunks;
     const int ctas = (warps + kWarpsPerCta - 1) / kWarpsPerCta;
-    fn<<<ctas, kWarpsPerCta * 32, 0, s>>>(*p);
+    // Programmatic dependent launch: the next pass may start scheduling CTAs while this one
+    // drains; every warp executes griddepcontrol.wait before its first global access, so the
+    // prologue (work-item mapping, masks, register clearing) overlaps the predecessor's tail.
+    static const bool pdl = !(getenv("B200CONV_PDL") && atoi(getenv("B200CONV_PDL")) == 0);
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(ctas);
+    cfg.blockDim = dim3(kWarpsPerCta * 32);
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, fn, *p);
     count_launch(1);
-    return cudaGetLastError();
+    return e != cudaSuccess ? e : cudaGetLastError();
 }
 
 static cudaError_t stream_op(int op, const PassParams *p, int k, int strip_bytes, int ch, bool check, cudaStream_t s,

@@ -413,6 +413,14 @@ __device__ __forceinline__ void stream_warp(const PassParams &p, const int wid, 
                       (p.zero_n && in_r0 < 0) || (p.zero_s && in_r1 > p.rows);
     const bool partial = (p.bw % SB) != 0 && (band + 1) * p.vw >= p.bw;  // owns the cut last strip
 
+    // Programmatic dependent launch: everything above ran while the previous pass was still
+    // draining.  Let the pass after this one start scheduling, then wait until the previous
+    // pass (which wrote our source buffer) has completed and flushed.  Both are no-ops for
+    // launches without the programmatic-serialization attribute.
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    if (p.converged && *p.converged) return;  // fixed point already reached: nothing changes any more
+
     bool top = false, bot = false, west = false, east = false;
     const HaloParams &h = p.halo;
     if (h.enabled) {
@@ -474,7 +482,6 @@ stream_kernel(const PassParams p) {
     const int lane = threadIdx.x & 31;
     const int wid = blockIdx.x * kWarpsPerCta + (threadIdx.x >> 5);
     if (wid >= p.nbands * p.nchunks) return;
-    if (p.converged && *p.converged) return;  // fixed point already reached: nothing changes any more
     stream_warp<K, NW, CH, CHECK>(p, wid, lane, [&]() { return LdgFeed<NW>(p, lane); });
 }
 

@@ -127,7 +127,6 @@ stream_tma_kernel(const __grid_constant__ CUtensorMap tm, const PassParams p, co
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int wid = blockIdx.x * kWarpsPerCta + warp;
     if (wid >= p.nbands * p.nchunks) return;
-    if (p.converged && *p.converged) return;
     constexpr int kStage = TmaFeed<NW>::kStage;
     const uint32_t ring = smem_u32(smem) + (uint32_t)(warp * depth) * kStage;
     const uint32_t bars = smem_u32(smem) + (uint32_t)(kWarpsPerCta * depth) * kStage + (uint32_t)(warp * depth) * 8u;
@@ -214,9 +213,21 @@ static cudaError_t tma_op_t(int op, TmaState *t, const PassParams *p, int src_in
     if (op == 1) return cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ_out, fn, kWarpsPerCta * 32, smem);
     const int warps = p->nbands * p->nchunks;
     const int ctas = (warps + kWarpsPerCta - 1) / kWarpsPerCta;
-    fn<<<ctas, kWarpsPerCta * 32, smem, s>>>(t->map[src_index][NW == 1 ? 0 : 1], *p, depth);
+    // programmatic dependent launch, as for the LDG kernel (kernels.cu)
+    static const bool pdl = !(getenv("B200CONV_PDL") && atoi(getenv("B200CONV_PDL")) == 0);
+    cudaLaunchConfig_t lc{};
+    lc.gridDim = dim3(ctas);
+    lc.blockDim = dim3(kWarpsPerCta * 32);
+    lc.dynamicSmemBytes = smem;
+    lc.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    lc.attrs = attr;
+    lc.numAttrs = pdl ? 1 : 0;
+    cudaError_t e = cudaLaunchKernelEx(&lc, fn, t->map[src_index][NW == 1 ? 0 : 1], *p, depth);
     count_launch(1);
-    return cudaGetLastError();
+    return e != cudaSuccess ? e : cudaGetLastError();
 }
 
 static cudaError_t tma_op(int op, TmaState *t, const PassParams *p, int src_index, int k, int strip_bytes, int ch,

@@ -58,13 +58,17 @@ def test_grey_binary_equals_cuda_compat_mode(ref_cuda, tmp_path, reps):
 
 
 def test_rgb_binary_matches_linear_wrap_model(ref_cuda, tmp_path):
+    # Measured on B200: cudaMalloc places the reference's two 9216-byte buffers back to back, so
+    # its out-of-bounds rows H, H+1 of one buffer ARE rows 0, 1 of the other (and it races on them
+    # inside one launch).  Junk therefore creeps in from the bottom AND the top, one row per
+    # iteration; rows farther than that from both ends must equal the linear-wrap model.
     img = np.random.default_rng(7).integers(0, 256, (64, 48, 3), dtype=np.uint8)
     for reps in (2, 6):
         ref = run_ref(ref_cuda, tmp_path, img, reps)
         ours = blur(torch.from_numpy(img).cuda(), reps, boundary="cuda-compat").cpu().numpy()
-        # rows that cannot have seen out-of-bounds memory within `reps` iterations
-        safe = img.shape[0] - 1 - reps
-        assert (ours[:safe] == ref[:safe]).all()
+        lo, hi = reps + 2, img.shape[0] - 2 - reps
+        assert (ours[lo:hi] == ref[lo:hi]).all()
+        assert (ours == reference_oracle(img, reps, "cuda-compat")).all()
 
 
 def test_interior_of_binary_equals_default_mode_far_from_border(ref_cuda, tmp_path):
