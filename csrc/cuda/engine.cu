@@ -536,6 +536,19 @@ int b2c_engine_import(b2c_engine *e, const void *blobs, int n) {
     return B2C_OK;
 }
 
+int b2c_engine_disconnect(b2c_engine *e) {
+    if (!e) return B2C_EINVAL;
+    CK(cudaSetDevice(e->device));
+    CK(cudaDeviceSynchronize());
+    for (void *p : e->ipc_opened) cudaIpcCloseMemHandle(p);
+    e->ipc_opened.clear();
+    memset(e->peer_base, 0, sizeof e->peer_base);
+    memset(e->peer_pad, 0, sizeof e->peer_pad);
+    memset(e->rank_pad, 0, sizeof e->rank_pad);
+    e->connected = false;
+    return B2C_OK;
+}
+
 int b2c_engine_connect_local(b2c_engine **engines, int n) {
     if (!engines || n <= 0 || n != engines[0]->P * engines[0]->Q) {
         set_error("connect_local: need one engine per rank");

@@ -185,7 +185,12 @@ int worker(const b2c_cli &cli, int rank, int n, int P, int Q, Shared *sh) {
     sh->phase_ms[rank][4] = wr_ms;
     sh->iterations[rank] = executed;
     b2c_engine_describe(e, sh->plan[rank], sizeof sh->plan[rank]);
-    if (n > 1 && !barrier(sh, n)) return 1;  // nobody unmaps while a peer may still write
+    if (n > 1) {
+        // cudaIpc tear-down order: all writes done -> everyone unmaps -> everyone frees
+        if (!barrier(sh, n)) return 1;
+        WB2C(b2c_engine_disconnect(e));
+        if (!barrier(sh, n)) return 1;
+    }
     b2c_engine_destroy(e);
     cudaFreeHost(host);
     return 0;

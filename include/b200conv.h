@@ -169,6 +169,10 @@ int b2c_engine_block(const b2c_engine *e, int *row0, int *col0, int *rows, int *
 int b2c_engine_export(b2c_engine *e, void *blob /* B2C_HANDLE_BYTES */);
 int b2c_engine_import(b2c_engine *e, const void *blobs /* n * B2C_HANDLE_BYTES */, int n);
 int b2c_engine_connect_local(b2c_engine **engines, int n);
+/* Unmap every imported peer buffer.  Tear-down order for cudaIpc peers (freeing exported
+ * memory that a peer still has mapped is undefined behaviour): every rank disconnects ->
+ * host-level barrier -> every rank destroys its engine. */
+int b2c_engine_disconnect(b2c_engine *e);
 
 /* Data movement for this rank's block (tight or pitched host/device memory). */
 int b2c_engine_upload(b2c_engine *e, const uint8_t *host, int64_t pitch, void *stream);

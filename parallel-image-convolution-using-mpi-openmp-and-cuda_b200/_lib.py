@@ -76,6 +76,7 @@ def _load() -> C.CDLL:
         "b2c_engine_export": (I, [P, V]),
         "b2c_engine_import": (I, [P, V, I]),
         "b2c_engine_connect_local": (I, [C.POINTER(P), I]),
+        "b2c_engine_disconnect": (I, [P]),
         "b2c_engine_upload": (I, [P, u8p, L, V]),
         "b2c_engine_download": (I, [P, u8p, L, V]),
         "b2c_engine_load_device": (I, [P, u8p, L, V]),

@@ -93,6 +93,10 @@ class Engine:
         arr = (C.c_void_p * len(engines))(*[e._h for e in engines])
         check(lib.b2c_engine_connect_local(arr, len(engines)), "engine_connect_local")
 
+    def disconnect(self):
+        """Unmap imported peer buffers (every rank, then a barrier, then close())."""
+        check(lib.b2c_engine_disconnect(self._h), "engine_disconnect")
+
     def set_delay(self, cycles: int):
         check(lib.b2c_engine_set_delay(self._h, int(cycles)))
 

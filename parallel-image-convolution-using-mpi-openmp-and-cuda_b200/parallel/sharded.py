@@ -50,9 +50,15 @@ class ShardedBlur:
         return self.engine.block_shape
 
     def close(self):
+        # cudaIpc tear-down order: (1) nobody may still be writing into a peer -> barrier,
+        # (2) every rank unmaps its imports, (3) barrier, (4) only then free the exported memory
+        # (freeing memory a peer still has mapped is undefined behaviour and did corrupt later
+        # engines on 8 GPUs).
         torch.cuda.synchronize(self.device)
         if self.world > 1:
-            dist.barrier(group=self.group)  # nobody unmaps while a peer may still write
+            dist.barrier(group=self.group)
+            self.engine.disconnect()
+            dist.barrier(group=self.group)
         self.engine.close()
 
     def load(self, block: torch.Tensor):

@@ -14,3 +14,11 @@ timeout 600 $TR --master-port 29604 bench.py --gpus $N --steps 2 --warmup 3 --we
 echo "== nccl baseline"
 timeout 600 $TR --master-port 29605 scripts/nccl_baseline_bench.py --check 2>&1 | grep -E "$F" | tee gpurun_out/nccl_baseline_$N.json
 timeout 300 python -m pytest tests/test_launcher.py -m gpu -q -k multi 2>&1 | tail -2
+echo "== launcher, plumbing config (1920x2520 rgb, 40 reps) on $N GPUs"
+python - <<'PY'
+import sys
+sys.path.insert(0, ".")
+from b200conv.utils import waterfall_image, write_raw
+write_raw("/tmp/waterfall_1920_2520.raw", waterfall_image(2520, 1920, 3, seed=0))
+PY
+( cd /tmp && $GRAFT_REPO_ROOT/parallel-image-convolution-using-mpi-openmp-and-cuda_b200/lib/b200conv waterfall_1920_2520.raw 1920 2520 40 rgb --gpus $( [ $N -ge 4 ] && echo 4 || echo $N ) --profile --json $GRAFT_REPO_ROOT/gpurun_out/launcher_plumbing_$N.json 2>&1 | tail -8 )

@@ -70,3 +70,23 @@ def test_long_run_many_epochs():
     img = rnd(128, 256, 1, seed=12)
     want = reference_oracle(img, 203, "torus")
     assert (run_grid(img, (2, 2), 203, boundary="torus", tb=4, strip_bytes=4) == want).all()
+
+
+@pytest.mark.parametrize("boundary", ["zero", "torus"])
+@pytest.mark.parametrize("grid,hw", [((2, 2), (8, 8)), ((4, 2), (8, 6)), ((2, 4), (4, 16)), ((1, 2), (5, 32)),
+                                     ((2, 1), (6, 7)), ((3, 3), (9, 9))])
+def test_tiny_blocks_clamp_the_halo_depth(boundary, grid, hw):
+    """Blocks smaller than the requested fusion depth: a k-deep halo can only come from the
+    adjacent rank, so the engine lowers k (mpi_convolution.c has k=1 throughout)."""
+    for ch in (1, 3):
+        img = rnd(hw[0], hw[1], ch, seed=hw[0] + hw[1])
+        want = reference_oracle(img, 7, boundary)
+        assert (run_grid(img, grid, 7, boundary=boundary, tb=8) == want).all()
+
+
+def test_torus_one_rank_wraps_onto_itself():
+    import b200conv
+    for hw in ((4, 4), (9, 33), (64, 200)):
+        img = rnd(hw[0], hw[1], 3, seed=hw[1])
+        out = b200conv.blur(torch.from_numpy(img).cuda(), 9, boundary="torus", tb=4).cpu().numpy()
+        assert (out == reference_oracle(img, 9, "torus")).all()
