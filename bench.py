@@ -208,7 +208,8 @@ def run_b200conv(a):
         except Exception:
             pass
         out = {
-            "metric": "gigapixel-iterations/sec (device-timed, max over ranks)",
+            "metric": "gigapixel-iterations/sec",
+            "timer": "CUDA events around the iteration loop, max over ranks (mpi_convolution.c:151-154,242,264-275)",
             "value": value, "unit": "Gpix-it/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
             "ms_per_step": ms, "higher_is_better": True, "scaling": "weak" if a.weak else "strong",
             "vs_baseline": value / PUBLISHED[a.color], "dtype": "uint8 (exact integer; reference computes in fp32/fp64)",
