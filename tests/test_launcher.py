@@ -84,3 +84,13 @@ def test_multi_gpu_program(launcher, tmp_path):
         assert p.returncode == 0, p.stderr
         float(p.stdout.strip().splitlines()[0])
         assert (read_raw(tmp_path / "blur_m.raw", 512, 256, 3) == reference_oracle(img, 23, boundary)).all()
+
+
+@pytest.mark.gpu
+def test_worker_failure_takes_the_job_down(launcher, tmp_path):
+    """Failure detection: a worker that cannot read its block makes the launcher exit 1
+    (the reference would loop forever on a short file, cuda/functions.c:39-45)."""
+    (tmp_path / "short.raw").write_bytes(b"\x07" * 1000)
+    p = run(["short.raw", 64, 64, 3, "grey", "--gpus", 1], tmp_path)
+    assert p.returncode == 1
+    assert "short read" in p.stderr and "a worker failed" in p.stderr
