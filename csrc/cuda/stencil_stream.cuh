@@ -247,9 +247,12 @@ __device__ __forceinline__ void stream_band(const PassParams &p, Feed &feed, con
             hsum<NW, CH>(E, O, st.E[TM][j], st.O[TM][j]);
 #pragma unroll
             for (int i = 0; i < NW; ++i) {
+                // v of row r-j-1 (16-bit lanes).  The even lanes use a three-input add of the old
+                // values (IADD3, ALU pipe), the odd lanes add the freshly updated sum (ptxas picks
+                // IMAD.IADD, FMA-heavy pipe): keeps the two integer pipes evenly loaded.
+                E[i] = st.E[SP][j][i] + st.E[HP][j][i] + st.E[TM][j][i];
                 st.E[HP][j][i] += st.E[TM][j][i];   // h(r-1) + h(r): next row's sp
                 st.O[HP][j][i] += st.O[TM][j][i];
-                E[i] = st.E[SP][j][i] + st.E[HP][j][i];  // v of row r-j-1 (16-bit lanes)
                 O[i] = st.O[SP][j][i] + st.O[HP][j][i];
             }
             if (j + 1 < K) {
