@@ -63,6 +63,7 @@ struct TmaFeed {
     const uint32_t ring, bars;
     const int depth;
     int cx, cy, ngroups, g;
+    uint32_t a[NW], b[NW], c[NW];   // the three rows of the current group
 
     __device__ __forceinline__ TmaFeed(const CUtensorMap *tm_, int lane_, uint32_t ring_, uint32_t bars_, int depth_)
         : tm(tm_), lane(lane_), ring(ring_), bars(bars_), depth(depth_) {}
@@ -90,7 +91,10 @@ struct TmaFeed {
         __syncwarp();
     }
 
-    __device__ __forceinline__ void fetch3(int, uint32_t (&w0)[NW], uint32_t (&w1)[NW], uint32_t (&w2)[NW]) {
+    __device__ __forceinline__ void refill_a() {}
+    __device__ __forceinline__ void refill_b() {}
+    __device__ __forceinline__ void refill_c() {}
+    __device__ __forceinline__ void group(int) {
         // The previous group's rows have been consumed from registers: its stage can be refilled.
         if (g >= 1 && g - 1 + depth < ngroups) {
             __syncwarp();
@@ -102,11 +106,11 @@ struct TmaFeed {
         const int slot = g % depth;
         mbar_wait(bars + 8u * slot, (uint32_t)((g / depth) & 1));
         constexpr int kLanesPerBox = kBox / SB;
-        const uint32_t a = ring + (uint32_t)slot * kStage + (lane / kLanesPerBox) * (kTmaRows * kBox) +
-                           (lane % kLanesPerBox) * SB;
-        lds(a, w0);
-        lds(a + kBox, w1);
-        lds(a + 2 * kBox, w2);
+        const uint32_t sa = ring + (uint32_t)slot * kStage + (lane / kLanesPerBox) * (kTmaRows * kBox) +
+                            (lane % kLanesPerBox) * SB;
+        lds(sa, a);
+        lds(sa + kBox, b);
+        lds(sa + 2 * kBox, c);
         ++g;
     }
 
