@@ -674,6 +674,10 @@ int b2c_engine_run(b2c_engine *e, int reps, void *stream) {
         const auto key = std::make_pair(reps, e->cur);
         auto it = e->graphs.find(key);
         if (it == e->graphs.end()) {
+            if (e->graphs.size() >= 16) {  // callers that vary `reps` endlessly must not hoard graphs
+                for (auto &g : e->graphs) cudaGraphExecDestroy(g.second);
+                e->graphs.clear();
+            }
             const int cur0 = e->cur;
             const long long l0 = e->launches, g0 = total_launches();
             cudaGraph_t g;
