@@ -350,6 +350,68 @@ void choose_plan(b2c_engine *e) {
     if (e->kernel == B2C_KERNEL_NAIVE) e->F = 1;
 }
 
+// Rows per warp for large blocks are measured, not modelled: how the block scheduler packs
+// 4-6 waves of CTAs is not captured by plan_cost (160-row chunks beat 128-row ones by 4 % on
+// 16384² rgb, 112 beat 128 on grey).  A handful of candidates is timed on the engine's own (still
+// all-zero) buffers with the halo logic off: the kernel's time does not depend on pixel values,
+// zeros blur to zeros, and no frame or flag is touched.  ~10 ms once per engine; set
+// B200CONV_AUTOTUNE=0 or give chunk_rows explicitly to skip it.
+int autotune_chunk_rows(b2c_engine *e) {
+    static const bool off = getenv("B200CONV_AUTOTUNE") && atoi(getenv("B200CONV_AUTOTUNE")) == 0;
+    if (off || e->opts.chunk_rows > 0) return B2C_OK;
+    if (e->kernel != B2C_KERNEL_STREAM && e->kernel != B2C_KERNEL_TMA) return B2C_OK;
+    if ((double)e->bw * e->R * e->K < 512e6) return B2C_OK;   // small blocks: the model does well
+    static const int cand[] = {96, 112, 128, 144, 160, 192};
+    const bool any_nb = e->any_nb;
+    e->any_nb = false;
+    cudaStream_t s = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    int rc = B2C_OK, best = 0;
+    float best_ms = 1e30f;
+    if (cudaStreamCreate(&s) != cudaSuccess || cudaEventCreate(&ev0) != cudaSuccess ||
+        cudaEventCreate(&ev1) != cudaSuccess) {
+        set_error("autotune: %s", cudaGetErrorString(cudaGetLastError()));
+        rc = B2C_ECUDA;
+    }
+    const int sb0 = e->SB;
+    int best_sb = sb0;
+    for (int sb = 16; sb >= 8 && rc == B2C_OK; sb >>= 1) {
+        // also try the other strip width unless the caller fixed it (K*words <= 16 registers budget)
+        if (sb != sb0 && (e->opts.strip_bytes > 0 || e->K * (sb / 4) > 16)) continue;
+        e->SB = sb;
+        for (int c : cand) {
+            if (c > e->R) break;
+            e->opts.chunk_rows = c;
+            for (bool &ok : e->plan_ok) ok = false;
+            PassParams p;
+            fill_pass_params(e, e->K, false, 0, p);
+            cudaError_t ce = cudaSuccess;
+            for (int it = 0; it < 3 && ce == cudaSuccess; ++it) {
+                if (it == 1) cudaEventRecord(ev0, s);
+                ce = e->kernel == B2C_KERNEL_TMA ? launch_stream_tma(e->tma, p, 0, e->K, e->SB, e->CH, false, s)
+                                                 : launch_stream(p, e->K, e->SB, e->CH, false, s);
+            }
+            cudaEventRecord(ev1, s);
+            if (ce != cudaSuccess || cudaEventSynchronize(ev1) != cudaSuccess) {
+                set_error("autotune: %s", cudaGetErrorString(cudaGetLastError()));
+                rc = B2C_ECUDA;
+                break;
+            }
+            float ms = 0.f;
+            cudaEventElapsedTime(&ms, ev0, ev1);
+            if (ms < best_ms) { best_ms = ms; best = c; best_sb = sb; }
+        }
+    }
+    e->SB = best_sb;
+    if (ev0) cudaEventDestroy(ev0);
+    if (ev1) cudaEventDestroy(ev1);
+    if (s) cudaStreamDestroy(s);
+    e->any_nb = any_nb;
+    e->opts.chunk_rows = best;   // 0 (model) when nothing was timed
+    for (bool &ok : e->plan_ok) ok = false;
+    return rc;
+}
+
 int alloc_buffers(b2c_engine *e) {
     CK(cudaSetDevice(e->device));
     if (e->opts.boundary == B2C_CUDA_COMPAT) {
@@ -440,6 +502,10 @@ b2c_engine *b2c_engine_create(int device, int W, int H, int CH, int P, int Q, in
             b2c_engine_destroy(e);
             return nullptr;
         }
+    }
+    if (o.boundary != B2C_CUDA_COMPAT && autotune_chunk_rows(e) != B2C_OK) {
+        b2c_engine_destroy(e);
+        return nullptr;
     }
     // A torus rank that is its own neighbour in every direction needs no peers.
     bool self_only = e->any_nb;
