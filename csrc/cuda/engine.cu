@@ -360,8 +360,8 @@ int autotune_chunk_rows(b2c_engine *e) {
     static const bool off = getenv("B200CONV_AUTOTUNE") && atoi(getenv("B200CONV_AUTOTUNE")) == 0;
     if (off || e->opts.chunk_rows > 0) return B2C_OK;
     if (e->kernel != B2C_KERNEL_STREAM && e->kernel != B2C_KERNEL_TMA) return B2C_OK;
-    if ((double)e->bw * e->R * e->K < 512e6) return B2C_OK;   // small blocks: the model does well
-    static const int cand[] = {96, 112, 128, 144, 160, 192};
+    if ((double)e->bw * e->R < 16e6) return B2C_OK;   // passes of a few microseconds cannot be timed this way
+    static const int cand[] = {16, 24, 32, 48, 64, 80, 96, 112, 128, 144, 160, 192};
     const bool any_nb = e->any_nb;
     e->any_nb = false;
     cudaStream_t s = nullptr;
@@ -381,12 +381,15 @@ int autotune_chunk_rows(b2c_engine *e) {
         e->SB = sb;
         for (int c : cand) {
             if (c > e->R) break;
+            if (c < 2 * e->K) continue;                                   // pipeline fill would dominate
+            if (c < 64 && (double)e->bw * e->R >= 256e6) continue;        // pointless on large blocks
             e->opts.chunk_rows = c;
             for (bool &ok : e->plan_ok) ok = false;
             PassParams p;
             fill_pass_params(e, e->K, false, 0, p);
             cudaError_t ce = cudaSuccess;
-            for (int it = 0; it < 3 && ce == cudaSuccess; ++it) {
+            const int reps = (double)e->bw * e->R < 128e6 ? 9 : 3;   // short passes: average more of them
+            for (int it = 0; it < reps && ce == cudaSuccess; ++it) {
                 if (it == 1) cudaEventRecord(ev0, s);
                 ce = e->kernel == B2C_KERNEL_TMA ? launch_stream_tma(e->tma, p, 0, e->K, e->SB, e->CH, false, s)
                                                  : launch_stream(p, e->K, e->SB, e->CH, false, s);
