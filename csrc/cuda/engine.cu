@@ -360,8 +360,9 @@ int autotune_chunk_rows(b2c_engine *e) {
     static const bool off = getenv("B200CONV_AUTOTUNE") && atoi(getenv("B200CONV_AUTOTUNE")) == 0;
     if (off || e->opts.chunk_rows > 0) return B2C_OK;
     if (e->kernel != B2C_KERNEL_STREAM && e->kernel != B2C_KERNEL_TMA) return B2C_OK;
-    if ((double)e->bw * e->R < 16e6) return B2C_OK;   // passes of a few microseconds cannot be timed this way
-    static const int cand[] = {16, 24, 32, 48, 64, 80, 96, 112, 128, 144, 160, 192};
+    const double bytes = (double)e->bw * e->R;
+    if (bytes < 1e6) return B2C_OK;   // tiny images: a pass is shorter than the launch path, keep the model
+    static const int cand[] = {8, 12, 16, 24, 32, 48, 64, 80, 96, 112, 128, 144, 160, 192};
     const bool any_nb = e->any_nb;
     e->any_nb = false;
     cudaStream_t s = nullptr;
@@ -375,20 +376,21 @@ int autotune_chunk_rows(b2c_engine *e) {
     }
     const int sb0 = e->SB;
     int best_sb = sb0;
-    for (int sb = 16; sb >= 8 && rc == B2C_OK; sb >>= 1) {
+    for (int sb = 16; sb >= (bytes < 64e6 ? 4 : 8) && rc == B2C_OK; sb >>= 1) {
         // also try the other strip width unless the caller fixed it (K*words <= 16 registers budget)
         if (sb != sb0 && (e->opts.strip_bytes > 0 || e->K * (sb / 4) > 16)) continue;
         e->SB = sb;
         for (int c : cand) {
             if (c > e->R) break;
             if (c < 2 * e->K) continue;                                   // pipeline fill would dominate
-            if (c < 64 && (double)e->bw * e->R >= 256e6) continue;        // pointless on large blocks
+            if (c < 64 && bytes >= 256e6) continue;                       // pointless on large blocks
+            if (c > 48 && bytes < 16e6) continue;                         // and long chunks starve small ones
             e->opts.chunk_rows = c;
             for (bool &ok : e->plan_ok) ok = false;
             PassParams p;
             fill_pass_params(e, e->K, false, 0, p);
             cudaError_t ce = cudaSuccess;
-            const int reps = (double)e->bw * e->R < 128e6 ? 9 : 3;   // short passes: average more of them
+            const int reps = bytes < 16e6 ? 41 : (bytes < 128e6 ? 9 : 3);   // short passes: average more of them
             for (int it = 0; it < reps && ce == cudaSuccess; ++it) {
                 if (it == 1) cudaEventRecord(ev0, s);
                 ce = e->kernel == B2C_KERNEL_TMA ? launch_stream_tma(e->tma, p, 0, e->K, e->SB, e->CH, false, s)

@@ -23,5 +23,6 @@ def test_bench_json_contract():
     assert d["n_gpus"] == 1 and d["steps"] == 2 and d["warmup"] == 3 and d["higher_is_better"] is True
     assert d["value"] > 0 and d["gpu_launches"] == 2 * 4          # 16 reps = 4 passes of K=4 per step
     assert d["e2e"]["value"] > 0 and d["e2e"]["h2d_bytes_per_step"] == 2048 * 2048 * 3
-    assert d["e2e"]["value"] < d["value"] * 1.05                   # end to end can not beat the device loop
+    # (for images this small the pipelined end-to-end rate may exceed the single-stream device
+    #  rate: two engines on two streams fill a GPU that one latency-bound image cannot)
     assert set(d["clocks"]) >= {"sm_mhz", "sm_max_mhz", "reasons"}
