@@ -244,6 +244,7 @@ void fill_push_params(const b2c_engine *e, int buf_i, bool wait, PushParams &q) 
     q.post_epoch = e->epoch + 1;
     q.wait_epoch = e->epoch;
     q.wait_epoch_valid = wait ? 1 : 0;
+    q.converged = nullptr;   // only the per-pass fallback push (enqueue_pass) follows the convergence latch
     for (int d = 0; d < 8; ++d) {
         if (e->nb[d] < 0) continue;
         q.peer_dst[d] = e->peer_base[buf_i][d];
@@ -295,6 +296,7 @@ int enqueue_pass(b2c_engine *e, const Pass &ps, cudaStream_t s) {
         if (e->any_nb && !p.halo.push) {
             PushParams q;
             fill_push_params(e, e->cur ^ 1, false, q);
+            if (e->opts.check_every > 0) q.converged = e->pad + kPadConverged;
             CK(launch_halo_push(q, s));
             e->launches++;
         }
@@ -348,6 +350,8 @@ void choose_plan(b2c_engine *e) {
     e->SB = SB;
     e->F = e->any_nb ? K : 1;
     if (e->kernel == B2C_KERNEL_NAIVE) e->F = 1;
+    // the byte-per-thread kernel has no change detector: a check would always report "unchanged"
+    if (e->kernel == B2C_KERNEL_NAIVE) e->opts.check_every = 0;
 }
 
 // Rows per warp for large blocks are measured, not modelled: how the block scheduler packs

@@ -169,6 +169,9 @@ cudaError_t launch_compat(const uint8_t *src, uint8_t *dst, int W, int H, int ch
 __global__ void halo_push_kernel(const PushParams q) {
     const int d = blockIdx.y;
     if (!q.peer_dst[d]) return;
+    // After the convergence latch every pass is skipped on every rank; the ring pushes that
+    // follow them must be skipped too or they would publish epochs nobody computed.
+    if (q.converged && *q.converged) return;
     if (q.wait_epoch_valid && threadIdx.x == 0) {
         // Do not overwrite a frame the neighbour may still be reading.
         const long long t0 = clock64();

@@ -25,6 +25,7 @@ struct PushParams {
     uint32_t post_epoch;
     uint32_t wait_epoch;
     int wait_epoch_valid;
+    const unsigned int *converged;   // when set and non-zero the push is skipped (like the passes)
 };
 
 struct ConvergeParams {

@@ -141,7 +141,8 @@ typedef struct b2c_opts {
     int strip_bytes;  /* bytes per thread per row (4,8,16); 0 = auto       */
     int chunk_rows;   /* rows per warp stream; 0 = auto                    */
     int use_graph;    /* capture the pass loop in a CUDA graph: -1 auto, 0, 1 */
-    int check_every;  /* fused convergence check period in iterations, 0 = off */
+    int check_every;  /* fused convergence check period in iterations, 0 = off (ignored by the
+                         naive kernel and cuda-compat, which have no change detector) */
 } b2c_opts;
 
 void b2c_default_opts(b2c_opts *o);

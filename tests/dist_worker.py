@@ -26,6 +26,9 @@ def main():
         (512, 1024, 3, 40, "torus", dict(tb=4, kernel="tma")),
         (128, 256, 1, 6, "zero", dict(kernel="naive")),
         (256, 256, 1, 400, "torus", dict(tb=4, check_every=20)),   # fused convergence across ranks
+        # convergence on the fallback push path (unaligned width), and the same engine reloaded and
+        # run again: the exchange after a converged run must not be skipped by the stale latch
+        (120, 100, 1, 1000, "torus", dict(tb=2, check_every=20, twice=True)),
         (128, 512, 3, 1000, "torus", dict(tb=4, delay=20000)),      # 250 epochs with skewed ranks
         (128, 512, 3, 501, "zero", dict(tb=2, delay=50000)),
     ]
@@ -38,6 +41,7 @@ def main():
         except b200conv.B2CError:
             continue
         delay = opts.pop("delay", 0)
+        twice = opts.pop("twice", False)
         eng = b200conv.ShardedBlur(W, H, ch, boundary=boundary, **opts)
         if delay:
             # T3 stress: skew the ranks against each other before every flag wait so a
@@ -45,9 +49,10 @@ def main():
             eng.engine.set_delay(delay * (1 + (rank * 7) % 5))
         r0, c0, r, c = eng.block
         blk = torch.from_numpy(np.ascontiguousarray(img[r0:r0 + r, c0:c0 + c])).cuda()
-        eng.load(blk)
-        ms = eng.timed_run(reps)
-        iters = eng.iterations_done()
+        for _ in range(2 if twice else 1):
+            eng.load(blk)
+            ms = eng.timed_run(reps)
+            iters = eng.iterations_done()
         out = torch.empty_like(blk)
         eng.store(out)
         torch.cuda.synchronize()

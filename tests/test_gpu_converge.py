@@ -37,3 +37,11 @@ def test_check_without_convergence_runs_everything():
     out, iters = blur(torch.from_numpy(img).cuda(), 30, check_every=10, return_iterations=True)
     assert iters == 30
     assert (out.cpu().numpy() == reference_oracle(img, 30, "zero")).all()
+
+
+def test_naive_kernel_ignores_check_every():
+    # the naive kernel has no change detector: check_every must be ignored, not read as "nothing changed"
+    img = rnd(64, 96, 1, seed=5)
+    out, iters = blur(torch.from_numpy(img).cuda(), 12, kernel="naive", check_every=4, return_iterations=True)
+    assert iters == 12
+    assert (out.cpu().numpy() == reference_oracle(img, 12, "zero")).all()
