@@ -5,6 +5,7 @@
 #include <cstdio>
 #include <cstring>
 #include <string>
+#include <vector>
 
 #include "b200conv.h"
 
@@ -31,5 +32,9 @@ inline int opposite_dir(int d) {
     static const int opp[8] = {B2C_S, B2C_N, B2C_E, B2C_W, B2C_SE, B2C_SW, B2C_NE, B2C_NW};
     return opp[d];
 }
+
+// oracle.cpp: k Gaussian iterations over one rank's framed buffer (used by both host models).
+void framed_iterations(std::vector<uint8_t> &t0, std::vector<uint8_t> &t1, int rows, int64_t pitch, int ch, int F,
+                       int64_t fb, int r0, int64_t c0b, int H, int64_t Wb, bool torus, int k);
 
 }  // namespace b2c

@@ -1,0 +1,249 @@
+// Host model of the multi-GPU protocol ("host emulation of the halo protocol
+// (threads + the same slot/flag state machine) to test epoch logic without GPUs").
+//
+// One thread plays one rank.  The state machine is the engine's (csrc/cuda/engine.cu,
+// stencil_stream.cuh, kernels.cu: converge_kernel), restated with std::atomic:
+//
+//   * two framed ping-pong buffers per rank; pass t reads buf[(t-1)&1] and writes buf[t&1];
+//   * after a pass a rank stores the depth-F ring of its new block straight into the frames of
+//     its (up to 8) neighbours' buf[t&1], then release-stores epoch t+1 into the flag word the
+//     neighbour keeps for that direction;
+//   * before a pass a rank acquire-waits on the flag of every direction that has a neighbour —
+//     that covers both "my halos have arrived" and "the neighbour has finished reading the frame
+//     I am about to overwrite";
+//   * ring results are published before the interior is written (the GPU orders ring warps first);
+//   * a check pass is followed by an all-to-all exchange of one "changed" bit through per-rank
+//     slots tagged with the check number and double-buffered by its parity; when nobody changed,
+//     every rank latches `converged` and skips the remaining passes.
+//
+// Random sleeps can be injected at every point where the GPU ranks may drift apart.  Built with
+// -fsanitize=thread (tests/test_halo_model.py) the model shows that the protocol has no data race
+// on the frames; with `single_slot_set` it reproduces the lost-tag hang that the parity fixes.
+// Nothing here is taken from the reference: mpi_convolution.c:158-234 has neither epochs, nor
+// diagonal neighbours, nor a convergence test.
+#include <atomic>
+#include <chrono>
+#include <memory>
+#include <random>
+#include <thread>
+#include <vector>
+
+#include "common.h"
+
+namespace {
+
+using Clock = std::chrono::steady_clock;
+
+struct Rank {
+    std::vector<uint8_t> buf[2];
+    int nb[8];
+    std::atomic<uint32_t> flag[8];
+    std::unique_ptr<std::atomic<uint32_t>[]> slots;  // 2 sets x n ranks
+    int iters = 0;
+    int final_buf = 0;
+};
+
+struct Pass {
+    int k;
+    bool check;
+    int iters_after;
+};
+
+// Same rule as make_passes() in engine.cu: k in {K, K/2, .., 1}, a pass ends on every multiple of
+// check_every.
+std::vector<Pass> split_passes(int reps, int K, int ce) {
+    std::vector<Pass> v;
+    int done = 0;
+    while (done < reps) {
+        int limit = reps - done;
+        if (ce > 0) limit = std::min(limit, ce - done % ce);
+        int k = K;
+        while (k > limit) k >>= 1;
+        done += k;
+        v.push_back({k, ce > 0 && done % ce == 0, done});
+    }
+    return v;
+}
+
+struct World {
+    int W, H, ch, P, Q, R, C, F, n;
+    int64_t bw, fb, pitch;
+    int rows;
+    bool torus;
+    b2c_emul_opts o;
+    std::vector<Pass> passes;
+    std::vector<Rank> ranks;
+    std::atomic<int> arrived{0};
+    std::atomic<bool> failed{false};
+    Clock::time_point deadline;
+
+    // Spin until pred() or the deadline; a timeout marks the whole run as failed.
+    template <class Pred>
+    bool wait_for(Pred pred) {
+        while (!pred()) {
+            if (failed.load(std::memory_order_relaxed)) return false;
+            if (Clock::now() > deadline) {
+                failed.store(true);
+                return false;
+            }
+            std::this_thread::yield();
+        }
+        return true;
+    }
+
+    void push_ring(int q, int par) {
+        Rank &me = ranks[q];
+        for (int d = 0; d < 8; ++d) {
+            const int nb = me.nb[d];
+            if (nb < 0) continue;
+            const int dr = b2c::kDirDr[d], dc = b2c::kDirDc[d];
+            const int sr0 = dr > 0 ? R - F : 0, nr = dr ? F : R;
+            const int64_t sc0 = dc > 0 ? bw - fb : 0, nc = dc ? fb : bw;
+            const int tr0 = sr0 - dr * R;
+            const int64_t tc0 = sc0 - dc * bw;
+            for (int r = 0; r < nr; ++r)
+                memcpy(&ranks[nb].buf[par][(tr0 + r + F) * pitch + fb + tc0],
+                       &me.buf[par][(sr0 + r + F) * pitch + fb + sc0], (size_t)nc);
+        }
+    }
+
+    void publish(int q, uint32_t epoch) {
+        Rank &me = ranks[q];
+        for (int d = 0; d < 8; ++d)
+            if (me.nb[d] >= 0) ranks[me.nb[d]].flag[b2c::opposite_dir(d)].store(epoch, std::memory_order_release);
+    }
+
+    void run_rank(int q, const uint8_t *in) {
+        Rank &me = ranks[q];
+        std::mt19937 rng(o.seed * 7919u + (unsigned)q);
+        auto jitter = [&] {
+            if (o.max_delay_us > 0)
+                std::this_thread::sleep_for(std::chrono::microseconds(rng() % (unsigned)(o.max_delay_us + 1)));
+        };
+        const int r0 = (q / Q) * R, c0 = (q % Q) * C;
+        const int64_t c0b = (int64_t)(q % Q) * bw;
+
+        // "upload": the whole framed buffer is rewritten, so nobody may push before everyone is here
+        for (auto &b : me.buf) b.assign((size_t)(pitch * rows), 0);
+        for (int r = 0; r < R; ++r)
+            memcpy(&me.buf[0][(r + F) * pitch + fb], in + ((int64_t)(r0 + r) * W + c0) * ch, (size_t)bw);
+        arrived.fetch_add(1, std::memory_order_acq_rel);
+        if (!wait_for([&] { return arrived.load(std::memory_order_acquire) >= n; })) return;
+
+        // initial exchange = epoch 1
+        jitter();
+        push_ring(q, 0);
+        publish(q, 1);
+        uint32_t epoch = 1;
+        int cur = 0;
+        uint32_t seq = 0;
+        bool converged = false;
+        std::vector<uint8_t> t0, t1;
+        me.iters = passes.empty() ? 0 : passes.back().iters_after;
+
+        for (const Pass &ps : passes) {
+            unsigned changed = 0;
+            if (!converged) {
+                jitter();
+                for (int d = 0; d < 8; ++d)
+                    if (me.nb[d] >= 0 &&
+                        !wait_for([&] { return (int32_t)(me.flag[d].load(std::memory_order_acquire) - epoch) >= 0; }))
+                        return;
+                t0 = me.buf[cur];
+                b2c::framed_iterations(t0, t1, rows, pitch, ch, F, fb, r0, c0b, H, (int64_t)W * ch, torus, ps.k);
+                auto copy_rows = [&](int ra, int rb, int64_t xa, int64_t xb) {
+                    for (int r = ra; r < rb; ++r) {
+                        const int64_t off = (r + F) * pitch + fb;
+                        memcpy(&me.buf[cur ^ 1][off + xa], &t0[off + xa], (size_t)(xb - xa));
+                        if (ps.check) changed |= memcmp(&t0[off + xa], &t1[off + xa], (size_t)(xb - xa)) != 0;
+                    }
+                };
+                // ring first (top / bottom F rows, left / right fb bytes), then publish, then interior
+                const int Ft = std::min(F, R), Fb = std::max(Ft, R - F);
+                const int64_t fl = std::min(fb, bw), fr = std::max(fl, bw - fb);
+                copy_rows(0, Ft, 0, bw);
+                copy_rows(Fb, R, 0, bw);
+                copy_rows(Ft, Fb, 0, fl);
+                copy_rows(Ft, Fb, fr, bw);
+                jitter();
+                push_ring(q, cur ^ 1);
+                publish(q, epoch + 1);
+                jitter();
+                copy_rows(Ft, Fb, fl, fr);
+                cur ^= 1;
+                epoch++;
+            }
+            if (ps.check) {
+                ++seq;
+                const uint32_t tag = seq * 2u;
+                const int set = o.single_slot_set ? 0 : (int)(seq & 1u) * n;
+                for (int k = 0; k < n; ++k)
+                    ranks[k].slots[set + q].store(tag | (changed ? 1u : 0u), std::memory_order_release);
+                if (q == o.stall_rank && o.stall_ms > 0)
+                    std::this_thread::sleep_for(std::chrono::milliseconds(o.stall_ms));
+                else
+                    jitter();
+                unsigned any = 0;
+                for (int k = 0; k < n; ++k) {
+                    uint32_t v = 0;
+                    if (!wait_for([&] { return ((v = me.slots[set + k].load(std::memory_order_acquire)) & ~1u) == tag; }))
+                        return;
+                    any |= v & 1u;
+                }
+                if (!any && !converged) {
+                    converged = true;
+                    me.iters = ps.iters_after;
+                }
+            }
+        }
+        me.final_buf = cur;
+    }
+};
+
+}  // namespace
+
+extern "C" int b2c_emulate_halo_threads(const uint8_t *in, uint8_t *out, int W, int H, int ch, int reps, int boundary,
+                                        int P, int Q, const b2c_emul_opts *opts, int *iterations_done) {
+    if (!in || !out || !opts || W <= 0 || H <= 0 || (ch != 1 && ch != 3) || reps < 0 || P <= 0 || Q <= 0 || H % P ||
+        W % Q || P * Q > 64 || (boundary != B2C_ZERO && boundary != B2C_TORUS)) {
+        b2c::set_error("emulate_halo_threads: bad arguments");
+        return B2C_EINVAL;
+    }
+    World w;
+    w.W = W, w.H = H, w.ch = ch, w.P = P, w.Q = Q, w.R = H / P, w.C = W / Q, w.n = P * Q;
+    w.torus = boundary == B2C_TORUS;
+    w.o = *opts;
+    int K = opts->tb >= 8 ? 8 : (opts->tb >= 4 ? 4 : (opts->tb >= 2 ? 2 : 1));
+    while (K > 1 && K > std::min(w.R, w.C)) K >>= 1;  // a k-deep halo comes from the adjacent rank only
+    w.F = K;
+    w.bw = (int64_t)w.C * ch, w.fb = (int64_t)w.F * ch, w.pitch = w.bw + 2 * w.fb;
+    w.rows = w.R + 2 * w.F;
+    w.passes = split_passes(reps, K, opts->check_every);
+    w.ranks = std::vector<Rank>((size_t)w.n);
+    for (int q = 0; q < w.n; ++q) {
+        Rank &r = w.ranks[q];
+        b2c_neighbours(q, P, Q, boundary, r.nb);
+        for (auto &f : r.flag) f.store(0);
+        r.slots.reset(new std::atomic<uint32_t>[2 * (size_t)w.n]);
+        for (int k = 0; k < 2 * w.n; ++k) r.slots[k].store(0);
+    }
+    w.deadline = Clock::now() + std::chrono::milliseconds(opts->timeout_ms > 0 ? opts->timeout_ms : 20000);
+    std::vector<std::thread> th;
+    for (int q = 0; q < w.n; ++q) th.emplace_back([&w, q, in] { w.run_rank(q, in); });
+    for (auto &t : th) t.join();
+    if (w.failed.load()) {
+        b2c::set_error("emulate_halo_threads: a rank waited past the deadline (protocol deadlock)");
+        return B2C_ETIMEOUT;
+    }
+    for (int q = 0; q < w.n; ++q) {
+        const int r0 = (q / Q) * w.R, c0 = (q % Q) * w.C;
+        for (int r = 0; r < w.R; ++r)
+            memcpy(out + ((int64_t)(r0 + r) * W + c0) * ch, &w.ranks[q].buf[w.ranks[q].final_buf][(r + w.F) * w.pitch + w.fb], (size_t)w.bw);
+        if (w.ranks[q].iters != w.ranks[0].iters) {
+            b2c::set_error("emulate_halo_threads: ranks disagree on the iteration count");
+            return B2C_EINVAL;
+        }
+    }
+    if (iterations_done) *iterations_done = w.ranks[0].iters;
+    return B2C_OK;
+}

@@ -118,6 +118,31 @@ void blur_cuda_compat_rgb(const uint8_t *in, uint8_t *out, int W, int H, int rep
 
 }  // namespace
 
+namespace b2c {
+
+// k Gaussian iterations over one rank's framed buffer (frame = F rows / fb bytes of halo on every
+// side).  t0 holds the input and receives the result; t1 is scratch and ends up holding iteration
+// k-1.  Bytes that lie outside the global image stay 0 in ZERO mode, which is what makes the
+// valid region shrink correctly from pass to pass.  (r0, c0b) = global row / byte column of the
+// block's first pixel.
+void framed_iterations(std::vector<uint8_t> &t0, std::vector<uint8_t> &t1, int rows, int64_t pitch, int ch, int F,
+                       int64_t fb, int r0, int64_t c0b, int H, int64_t Wb, bool torus, int k) {
+    static const Weights w = make_weights(B2C_GAUSSIAN);
+    t1.assign(t0.size(), 0);
+    for (int s = 0; s < k; ++s) {
+        for (int r = 1; r < rows - 1; ++r)
+            for (int64_t x = ch; x < pitch - ch; ++x) {
+                const int gr = r0 + r - F;
+                const int64_t gx = c0b + x - fb;
+                const bool outside = gr < 0 || gr >= H || gx < 0 || gx >= Wb;
+                t1[r * pitch + x] = (!torus && outside) ? 0 : tap9(&t0[r * pitch + x], pitch, ch, w);
+            }
+        std::swap(t0, t1);
+    }
+}
+
+}  // namespace b2c
+
 extern "C" {
 
 int b2c_oracle_blur(const uint8_t *in, uint8_t *out, int W, int H, int ch, int reps, int boundary,
@@ -149,7 +174,6 @@ int b2c_oracle_blur_sharded(const uint8_t *in, uint8_t *out, int W, int H, int c
         b2c::set_error("oracle_blur_sharded: bad arguments");
         return B2C_EINVAL;
     }
-    const Weights w = make_weights(B2C_GAUSSIAN);
     const int n = P * Q, R = H / P, C = W / Q;
     const bool torus = boundary == B2C_TORUS;
     // A k-deep halo can only come from the adjacent rank, so k <= block size.
@@ -197,17 +221,7 @@ int b2c_oracle_blur_sharded(const uint8_t *in, uint8_t *out, int W, int H, int c
             const int r0 = (q / Q) * R;
             const int64_t c0b = (int64_t)(q % Q) * bw;
             t0 = rk.buf[par];
-            t1.assign(t0.size(), 0);
-            for (int s = 0; s < k; ++s) {
-                for (int r = 1; r < rows - 1; ++r)
-                    for (int64_t x = ch; x < pitch - ch; ++x) {
-                        int gr = r0 + r - F;
-                        int64_t gx = c0b + x - fb;
-                        bool outside = gr < 0 || gr >= H || gx < 0 || gx >= (int64_t)W * ch;
-                        t1[r * pitch + x] = (!torus && outside) ? 0 : tap9(&t0[r * pitch + x], pitch, ch, w);
-                    }
-                std::swap(t0, t1);
-            }
+            b2c::framed_iterations(t0, t1, rows, pitch, ch, F, fb, r0, c0b, H, (int64_t)W * ch, torus, k);
             for (int r = 0; r < R; ++r)
                 memcpy(&rk.buf[par ^ 1][(r + F) * pitch + fb], &t0[(r + F) * pitch + fb], (size_t)bw);
         }

@@ -44,12 +44,12 @@ struct NvtxRange {
 // Flag pad layout, in 32-bit words.  Every flag/counter sits on its own 128 B line.
 constexpr int kPadFlags = 0;          // 8 x 32
 constexpr int kPadCounters = 256;     // 8 x 32
-constexpr int kPadSlots = 512;        // up to 64 ranks
+constexpr int kPadSlots = 512;        // 2 parities x kMaxRanks words
 constexpr int kPadChanged = 640;
 constexpr int kPadConverged = 641;
 constexpr int kPadConvergedAt = 642;
 constexpr int kPadWords = 1024;
-constexpr int kMaxRanks = 64;
+static_assert(kPadSlots + 2 * kMaxRanks <= kPadChanged, "convergence slots overlap the next pad field");
 
 struct Blob {  // what b2c_engine_export ships; must fit B2C_HANDLE_BYTES
     cudaIpcMemHandle_t buf[2];

@@ -252,21 +252,30 @@ __global__ void set_u32_kernel(unsigned int *p, unsigned int v) { *p = v; }
 // Convergence bookkeeping after a CHECK pass: publish this rank's "changed"
 // bit to every rank, wait for all ranks' bits, and latch `converged` when the
 // OR is zero.  One thread; runs on the pass stream right after the CHECK pass.
+//
+// Slots are double-buffered by the parity of the check number.  With a single
+// set a fast rank could leave check s (it has seen everybody's tag s), run the
+// next pass, enter check s+1 and overwrite its word in a slow rank's array
+// before that rank has read tag s there — the slow rank would then wait for a
+// tag that no longer exists.  A rank can only write tag s+2 after it has seen
+// every rank's tag s+1, and a rank publishes s+1 after it finished reading s,
+// so two sets are enough.  (Found with the host model, csrc/core/halo_emul.cpp.)
 __global__ void converge_kernel(const ConvergeParams c) {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
     const unsigned mine = *c.changed;
     *c.changed = 0;
     // slot value = 2*seq + bit so that a slot from an older check never matches
     const unsigned tag = c.seq * 2u;
+    const int set = (int)(c.seq & 1u) * kMaxRanks;
     for (int k = 0; k < c.nranks; ++k) {
         __threadfence_system();
-        st_release_sys(c.peer_slots[k] + c.rank, tag | (mine ? 1u : 0u));
+        st_release_sys(c.peer_slots[k] + set + c.rank, tag | (mine ? 1u : 0u));
     }
     unsigned any = 0;
     for (int k = 0; k < c.nranks; ++k) {
         const long long t0 = clock64();
         unsigned v;
-        while (((v = ld_acquire_sys(c.slots + k)) & ~1u) != tag) {
+        while (((v = ld_acquire_sys(c.slots + set + k)) & ~1u) != tag) {
             if (clock64() - t0 > (20ll << 30)) {
                 printf("b200conv: convergence wait timeout rank=%d peer=%d\n", c.rank, k);
                 __trap();

@@ -28,10 +28,12 @@ struct PushParams {
     const unsigned int *converged;   // when set and non-zero the push is skipped (like the passes)
 };
 
+constexpr int kMaxRanks = 64;
+
 struct ConvergeParams {
     unsigned int *changed;        // this rank's OR-accumulated bit (reset here)
-    uint32_t *slots;              // our slot array, one word per rank
-    uint32_t *peer_slots[8];      // every rank's slot array (index = rank)
+    uint32_t *slots;              // our slot array: 2 parities x kMaxRanks words
+    uint32_t *peer_slots[kMaxRanks];  // every rank's slot array (index = rank)
     int nranks, rank;
     unsigned int seq;             // check sequence number (>= 1)
     unsigned int *converged;      // latched flag

@@ -54,7 +54,8 @@ enum {
     B2C_EIO = -3,
     B2C_ENOMEM = -4,
     B2C_ETOOBIG = -5,
-    B2C_EDIVIDE = -6
+    B2C_EDIVIDE = -6,
+    B2C_ETIMEOUT = -7
 };
 
 const char *b2c_last_error(void);
@@ -130,6 +131,29 @@ int b2c_oracle_blur(const uint8_t *in, uint8_t *out, int width, int height, int 
  * Result must equal b2c_oracle_blur on every grid (decomposition independence). */
 int b2c_oracle_blur_sharded(const uint8_t *in, uint8_t *out, int width, int height, int channels,
                             int repetitions, int boundary, int grid_rows, int grid_cols, int tb);
+
+/* Threaded host model of the multi-GPU protocol: one thread per rank, framed
+ * ping-pong buffers, per-direction epoch flags (release/acquire), ring pushes
+ * into the neighbours' frames, and the tagged-slot convergence exchange —
+ * the state machine of the GPU engine restated with std::atomic so that the
+ * epoch logic can be tested (and run under ThreadSanitizer) without a GPU.
+ * No counterpart in the reference. */
+typedef struct b2c_emul_opts {
+    int tb;              /* fused iterations per pass (1, 2, 4, 8)                         */
+    int check_every;     /* 0 = off                                                         */
+    int max_delay_us;    /* random sleep up to this long at every drift point; 0 = none     */
+    unsigned seed;       /* for the sleeps                                                  */
+    int timeout_ms;      /* a wait longer than this fails the run; 0 = 20 s                 */
+    int single_slot_set; /* 1 = model one convergence slot set instead of two (regression) */
+    int stall_rank;      /* this rank sleeps stall_ms between publishing and reading its    */
+    int stall_ms;        /*   convergence slots; -1 / 0 = nobody                            */
+} b2c_emul_opts;
+
+/* Returns B2C_OK (out = gathered image, *iterations_done = iterations run),
+ * B2C_EINVAL, or B2C_ETIMEOUT when a rank waited past the deadline. */
+int b2c_emulate_halo_threads(const uint8_t *in, uint8_t *out, int width, int height, int channels,
+                             int repetitions, int boundary, int grid_rows, int grid_cols,
+                             const b2c_emul_opts *opts, int *iterations_done);
 
 /* --------------------------------------------------------------- GPU engine */
 

@@ -32,6 +32,11 @@ class Opts(C.Structure):
                 ("boundary", "filter", "kernel", "tb", "strip_bytes", "chunk_rows", "use_graph", "check_every")]
 
 
+class EmulOpts(C.Structure):
+    _fields_ = [("tb", C.c_int), ("check_every", C.c_int), ("max_delay_us", C.c_int), ("seed", C.c_uint),
+                ("timeout_ms", C.c_int), ("single_slot_set", C.c_int), ("stall_rank", C.c_int), ("stall_ms", C.c_int)]
+
+
 class Cli(C.Structure):
     _fields_ = [("image", C.c_char_p), ("width", C.c_int), ("height", C.c_int), ("repetitions", C.c_int),
                 ("channels", C.c_int), ("gpus", C.c_int), ("boundary", C.c_int), ("filter", C.c_int),
@@ -69,6 +74,7 @@ def _load() -> C.CDLL:
         "b2c_write_block": (L, [C.c_char_p, u8p, L, I, I, I, I, I, I, I, I]),
         "b2c_oracle_blur": (I, [u8p, u8p, I, I, I, I, I, I]),
         "b2c_oracle_blur_sharded": (I, [u8p, u8p, I, I, I, I, I, I, I, I]),
+        "b2c_emulate_halo_threads": (I, [u8p, u8p, I, I, I, I, I, I, I, C.POINTER(EmulOpts), C.POINTER(I)]),
         "b2c_default_opts": (None, [C.POINTER(Opts)]),
         "b2c_engine_create": (P, [I, I, I, I, I, I, I, C.POINTER(Opts)]),
         "b2c_engine_destroy": (None, [P]),

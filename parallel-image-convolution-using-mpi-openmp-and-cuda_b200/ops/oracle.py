@@ -6,6 +6,8 @@
                         cross-check the C++ oracle (mpi/mpi_convolution.c:301-322 semantics at
                         one rank; torus per README.md:63-66).
 ``sharded_oracle``    — host emulation of the multi-rank frame/epoch halo protocol.
+``threaded_halo_model`` — the same protocol with one thread per rank, atomics for the epoch flags
+                        and the convergence slots, and injected delays (csrc/core/halo_emul.cpp).
 """
 from __future__ import annotations
 
@@ -52,6 +54,21 @@ def sharded_oracle(img, reps: int, grid, boundary: str = "zero", tb: int = 1):
     check(lib.b2c_oracle_blur_sharded(flat.ctypes.data, out.ctypes.data, w, h, ch, int(reps), BOUNDARY[boundary],
                                       int(grid[0]), int(grid[1]), int(tb)), "oracle_blur_sharded")
     return restore(out)
+
+
+def threaded_halo_model(img, reps: int, grid, boundary: str = "zero", tb: int = 1, check_every: int = 0,
+                        max_delay_us: int = 0, seed: int = 0, timeout_ms: int = 0, single_slot_set: bool = False,
+                        stall_rank: int = -1, stall_ms: int = 0):
+    """-> (image, iterations run).  Raises B2CError (code B2C_ETIMEOUT) when a rank deadlocks."""
+    flat, w, h, ch, restore = _as_image(img)
+    out = np.empty_like(flat)
+    o = _lib.EmulOpts(int(tb), int(check_every), int(max_delay_us), int(seed), int(timeout_ms),
+                      int(bool(single_slot_set)), int(stall_rank), int(stall_ms))
+    iters = C.c_int(0)
+    check(lib.b2c_emulate_halo_threads(flat.ctypes.data, out.ctypes.data, w, h, ch, int(reps), BOUNDARY[boundary],
+                                       int(grid[0]), int(grid[1]), C.byref(o), C.byref(iters)),
+          "emulate_halo_threads")
+    return restore(out), iters.value
 
 
 def numpy_oracle(img, reps: int, boundary: str = "zero"):

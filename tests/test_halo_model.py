@@ -1,0 +1,120 @@
+"""T3 without GPUs: the threaded host model of the halo / convergence protocol.
+
+One thread per rank, the engine's epoch-flag and tagged-slot state machine restated with
+std::atomic (csrc/core/halo_emul.cpp).  The result must equal the 1-rank oracle on every grid,
+with ranks skewed by random sleeps; the same sources built with -fsanitize=thread must report no
+data race; and the single-slot-set variant of the convergence exchange (what the GPU kernel used
+before the parity fix) must be caught as a deadlock.
+"""
+import shutil
+import subprocess
+import sys
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+from b200conv import B2CError, reference_oracle
+from b200conv.ops import threaded_halo_model
+
+ROOT = Path(__file__).resolve().parent.parent
+
+
+def rnd(h, w, ch, seed=0):
+    return np.random.default_rng(seed).integers(0, 256, (h, w) if ch == 1 else (h, w, ch), dtype=np.uint8)
+
+
+@pytest.mark.parametrize("grid", [(1, 1), (1, 2), (2, 1), (2, 2), (2, 4), (4, 2), (3, 3)])
+@pytest.mark.parametrize("boundary", ["zero", "torus"])
+@pytest.mark.parametrize("ch", [1, 3])
+def test_every_grid_gives_the_one_rank_result(grid, boundary, ch):
+    img = rnd(24, 24, ch, seed=1)                    # 24 divides by 1, 2, 3 and 4
+    for tb, reps in ((1, 5), (4, 11)):
+        out, iters = threaded_halo_model(img, reps, grid, boundary, tb=tb, max_delay_us=200, seed=tb)
+        assert iters == reps
+        assert (out == reference_oracle(img, reps, boundary)).all(), (grid, boundary, ch, tb)
+
+
+def test_many_epochs_with_skewed_ranks():
+    # 250 passes; each rank sleeps a different random time at every point where GPUs may drift apart
+    img = rnd(16, 32, 3, seed=2)
+    out, iters = threaded_halo_model(img, 500, (2, 4), "torus", tb=2, max_delay_us=300, seed=5)
+    assert iters == 500 and (out == reference_oracle(img, 500, "torus")).all()
+
+
+def test_halo_depth_is_clamped_to_the_block():
+    img = rnd(4, 8, 1, seed=3)                      # 2x2 blocks on a 2x4 grid: tb=8 must clamp to 2
+    out, _ = threaded_halo_model(img, 9, (2, 4), "torus", tb=8)
+    assert (out == reference_oracle(img, 9, "torus")).all()
+
+
+@pytest.mark.parametrize("grid", [(1, 1), (1, 2), (2, 2), (1, 4)])
+@pytest.mark.parametrize("boundary", ["zero", "torus"])
+def test_convergence_is_detected_by_every_rank_at_the_same_check(grid, boundary):
+    img = rnd(32, 32, 1, seed=4)
+    want = reference_oracle(img, 1000, boundary)
+    out, iters = threaded_halo_model(img, 1000, grid, boundary, tb=4, check_every=4, max_delay_us=100, seed=9)
+    assert iters < 1000 and iters % 4 == 0
+    assert (out == want).all()
+    assert (reference_oracle(want, 1, boundary) == want).all()
+
+
+def test_single_slot_set_loses_a_tag_and_two_sets_do_not():
+    # every pass is a check; rank 0 stalls between publishing and reading its slots, so rank 1
+    # reaches the next check first.  With one slot set rank 0 then never sees the tag it waits for.
+    img = rnd(16, 16, 1, seed=6)
+    kw = dict(tb=4, check_every=4, stall_rank=0, stall_ms=100, timeout_ms=1500)
+    with pytest.raises(B2CError, match="deadline"):
+        threaded_halo_model(img, 16, (1, 2), "torus", single_slot_set=True, **kw)
+    out, iters = threaded_halo_model(img, 16, (1, 2), "torus", **kw)
+    assert iters == 16 and (out == reference_oracle(img, 16, "torus")).all()
+
+
+TSAN_MAIN = r"""
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+#include "b200conv.h"
+int main() {
+    const int W = 24, H = 16, reps = 40;
+    int bad = 0;
+    for (int ch = 1; ch <= 3; ch += 2)
+        for (int boundary = 0; boundary <= 1; ++boundary) {
+            std::vector<uint8_t> in((size_t)W * H * ch), want(in.size()), got(in.size());
+            srand(7);
+            for (auto &b : in) b = (uint8_t)rand();
+            b2c_oracle_blur(in.data(), want.data(), W, H, ch, reps, boundary, B2C_GAUSSIAN);
+            b2c_emul_opts o;
+            memset(&o, 0, sizeof o);
+            o.tb = 4, o.max_delay_us = 50, o.seed = 3, o.stall_rank = -1;
+            int iters = 0;
+            int rc = b2c_emulate_halo_threads(in.data(), got.data(), W, H, ch, reps, boundary, 2, 4, &o, &iters);
+            bad += rc != B2C_OK || memcmp(want.data(), got.data(), got.size()) != 0;
+            o.check_every = 4;   // convergence exchange under the race detector as well
+            rc = b2c_emulate_halo_threads(in.data(), got.data(), W, H, ch, 400, boundary, 2, 2, &o, &iters);
+            b2c_oracle_blur(in.data(), want.data(), W, H, ch, iters, boundary, B2C_GAUSSIAN);
+            bad += rc != B2C_OK || memcmp(want.data(), got.data(), got.size()) != 0;
+        }
+    printf("bad=%d\n", bad);
+    return bad != 0;
+}
+"""
+
+
+@pytest.mark.skipif(shutil.which("g++") is None, reason="needs g++")
+def test_model_is_race_free_under_thread_sanitizer(tmp_path):
+    main = tmp_path / "main.cpp"
+    main.write_text(TSAN_MAIN)
+    exe = tmp_path / "halo_tsan"
+    srcs = [str(ROOT / "csrc/core" / f) for f in ("halo_emul.cpp", "oracle.cpp", "decomp.cpp")]
+    cmd = ["g++", "-std=c++17", "-O1", "-g", "-fsanitize=thread", "-pthread", "-I", str(ROOT / "include"),
+           "-I", str(ROOT / "csrc/core"), str(main), *srcs, "-o", str(exe)]
+    b = subprocess.run(cmd, capture_output=True, text=True)
+    if b.returncode != 0 and "tsan" in (b.stderr or "").lower():
+        pytest.skip("libtsan is not installed")
+    assert b.returncode == 0, b.stderr[-3000:]
+    r = subprocess.run([str(exe)], capture_output=True, text=True, timeout=600,
+                       env={"TSAN_OPTIONS": "halt_on_error=0 exitcode=66"})
+    assert "ThreadSanitizer" not in r.stderr, r.stderr[-4000:]
+    assert r.returncode == 0 and "bad=0" in r.stdout, (r.returncode, r.stdout, r.stderr[-2000:])
