@@ -574,6 +574,10 @@ int b2c_engine_import(b2c_engine *e, const void *blobs, int n) {
         set_error("engine_import: need %d blobs", e ? e->P * e->Q : 0);
         return B2C_EINVAL;
     }
+    if (e->connected) {
+        set_error("engine_import: already connected (b2c_engine_disconnect first)");
+        return B2C_EINVAL;
+    }
     CK(cudaSetDevice(e->device));
     std::vector<uint8_t *> rbuf0((size_t)n, nullptr), rbuf1((size_t)n, nullptr);
     const long long org = (long long)kFrameRows * e->pitch + kLeftPad;
@@ -629,7 +633,7 @@ int b2c_engine_disconnect(b2c_engine *e) {
 }
 
 int b2c_engine_connect_local(b2c_engine **engines, int n) {
-    if (!engines || n <= 0 || n != engines[0]->P * engines[0]->Q) {
+    if (!engines || n <= 0 || !engines[0] || n != engines[0]->P * engines[0]->Q) {
         set_error("connect_local: need one engine per rank");
         return B2C_EINVAL;
     }
@@ -661,8 +665,17 @@ int b2c_engine_connect_local(b2c_engine **engines, int n) {
     return B2C_OK;
 }
 
+// After a run with check_every the host's buffer index and epoch are only right once the
+// device-side latch has been read back.  Every entry point that depends on them settles first, so
+// a caller that skips b2c_engine_iterations_done still reads the right buffer.
+static int settle(b2c_engine *e) {
+    if (e->pending_converge_fixup && b2c_engine_iterations_done(e) < 0) return B2C_ECUDA;
+    return B2C_OK;
+}
+
 static int copy_block(b2c_engine *e, void *user, long long upitch, cudaMemcpyKind kind, bool to_engine, void *stream) {
     if (!e || !user) return B2C_EINVAL;
+    if (settle(e) != B2C_OK) return B2C_ECUDA;
     NvtxRange nvtx(to_engine ? "b2c_engine_load" : "b2c_engine_store");
     CK(cudaSetDevice(e->device));
     cudaStream_t s = (cudaStream_t)stream;
@@ -707,6 +720,7 @@ int b2c_engine_exchange(b2c_engine *e, void *stream) {
         set_error("engine_exchange: peers are not connected (import/connect_local first)");
         return B2C_EINVAL;
     }
+    if (settle(e) != B2C_OK) return B2C_ECUDA;
     CK(cudaSetDevice(e->device));
     PushParams q;
     fill_push_params(e, e->cur, false, q);
@@ -719,6 +733,7 @@ int b2c_engine_exchange(b2c_engine *e, void *stream) {
 int b2c_engine_run(b2c_engine *e, int reps, void *stream) {
     if (!e || reps < 0) return B2C_EINVAL;
     NvtxRange nvtx("b2c_engine_run");
+    if (settle(e) != B2C_OK) return B2C_ECUDA;
     CK(cudaSetDevice(e->device));
     cudaStream_t s = (cudaStream_t)stream;
     if (e->opts.boundary == B2C_CUDA_COMPAT) {
@@ -749,6 +764,13 @@ int b2c_engine_run(b2c_engine *e, int reps, void *stream) {
     }
     bool graph = e->opts.use_graph == 1 || (e->opts.use_graph < 0 && passes.size() >= 8);
     if (e->any_nb || e->opts.check_every > 0 || s == nullptr) graph = false;  // epochs are baked into params
+    if (graph) {  // a caller that is capturing this stream itself gets plain launches into its graph
+        cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+        if (cudaStreamIsCapturing(s, &cs) != cudaSuccess || cs != cudaStreamCaptureStatusNone) {
+            cudaGetLastError();
+            graph = false;
+        }
+    }
     if (graph) {
         const auto key = std::make_pair(reps, e->cur);
         auto it = e->graphs.find(key);
@@ -768,11 +790,15 @@ int b2c_engine_run(b2c_engine *e, int reps, void *stream) {
             e->cur = cur0;
             e->launches = l0;
             count_launch(g0 - total_launches());  // captured, not launched
-            if (rc != B2C_OK) return rc;
+            if (rc != B2C_OK) {
+                if (ce == cudaSuccess) cudaGraphDestroy(g);
+                return rc;
+            }
             CK(ce);
             cudaGraphExec_t ge;
-            CK(cudaGraphInstantiate(&ge, g, 0));
+            ce = cudaGraphInstantiate(&ge, g, 0);
             cudaGraphDestroy(g);
+            CK(ce);
             it = e->graphs.emplace(key, ge).first;
         }
         CK(cudaGraphLaunch(it->second, s));

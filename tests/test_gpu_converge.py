@@ -45,3 +45,25 @@ def test_naive_kernel_ignores_check_every():
     out, iters = blur(torch.from_numpy(img).cuda(), 12, kernel="naive", check_every=4, return_iterations=True)
     assert iters == 12
     assert (out.cpu().numpy() == reference_oracle(img, 12, "zero")).all()
+
+
+def test_store_settles_the_convergence_state_by_itself():
+    # a caller that never asks for the iteration count must still read the converged buffer, and a
+    # second run on the same engine must continue from it
+    from b200conv import Engine
+    img = rnd(128, 128, 1, seed=3)
+    want = reference_oracle(img, 1000, "torus")          # fixed point, reached long before 1000
+    eng = Engine(128, 128, 1, boundary="torus", check_every=20, tb=4)
+    src = torch.from_numpy(img).cuda()
+    out = torch.empty_like(src)
+    eng.load(src)
+    eng.exchange()                                        # torus: the rank is its own neighbour
+    eng.run(999)                                          # odd pass count: buffer index matters
+    eng.store(out)
+    torch.cuda.synchronize()
+    assert (out.cpu().numpy() == want).all()
+    eng.run(7)
+    eng.store(out)
+    torch.cuda.synchronize()
+    assert (out.cpu().numpy() == want).all()
+    eng.close()

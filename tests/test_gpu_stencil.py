@@ -152,3 +152,25 @@ def test_blur_pipeline_overlapped_steps():
     pipe.close()
     for x, d in zip(imgs, dsts):
         assert (d.numpy() == reference_oracle(x, 12, "zero")).all()
+
+
+def test_run_inside_a_callers_stream_capture():
+    # the engine normally wraps long runs in its own CUDA graph; when the caller is already
+    # capturing the stream it must fall back to plain launches that land in the caller's graph
+    from b200conv import Engine
+    img = np.random.default_rng(11).integers(0, 256, (256, 512, 3), dtype=np.uint8)
+    eng = Engine(512, 256, 3, tb=4)
+    src = torch.from_numpy(img).cuda()
+    out = torch.empty_like(src)
+    eng.load(src)
+    eng.run(4)                                            # first launch (kernel attribute set-up) outside the capture
+    eng.load(src)
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        eng.run(40)                                       # 10 passes: above the engine's own graph threshold
+    g.replay()
+    eng.store(out)
+    torch.cuda.synchronize()
+    assert (out.cpu().numpy() == reference_oracle(img, 40, "zero")).all()
+    eng.close()
