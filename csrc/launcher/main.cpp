@@ -196,6 +196,24 @@ int worker(const b2c_cli &cli, int rank, int n, int P, int Q, Shared *sh) {
     return 0;
 }
 
+// File names are arbitrary bytes: quote what JSON cannot carry verbatim.
+std::string json_escape(const char *in) {
+    std::string out;
+    for (const unsigned char *p = (const unsigned char *)in; *p; ++p) {
+        if (*p == '"' || *p == '\\') {
+            out += '\\';
+            out += (char)*p;
+        } else if (*p < 0x20) {
+            char buf[8];
+            snprintf(buf, sizeof buf, "\\u%04x", *p);
+            out += buf;
+        } else {
+            out += (char)*p;
+        }
+    }
+    return out;
+}
+
 void write_json(const b2c_cli &cli, int n, int P, int Q, const Shared *sh, double max_ms, double total_s) {
     FILE *f = fopen(cli.json, "w");
     if (!f) {
@@ -211,10 +229,11 @@ void write_json(const b2c_cli &cli, int n, int P, int Q, const Shared *sh, doubl
                "\"loop_seconds\": %.6f, \"total_seconds\": %.6f, \"gpix_it_per_s\": %.3f, "
                "\"hbm_bytes_per_iteration_k1\": %.0f, \"halo_bytes_per_gpu_per_iteration\": %d, "
                "\"pct_of_k1_hbm_roofline_6555GBs\": %.2f, \"plan\": \"%s\", \"per_rank_loop_ms\": [",
-            cli.image, cli.width, cli.height, cli.channels, cli.repetitions, it, n, P, Q, cli.boundary,
+            json_escape(cli.image).c_str(), cli.width, cli.height, cli.channels, cli.repetitions, it, n, P, Q,
+            cli.boundary,
             max_ms * 1e-3, total_s, gpix, 2.0 * cli.width * cli.height * cli.channels,
             n > 1 ? 2 * C * cli.channels + 2 * R * cli.channels + 4 * cli.channels : 0,
-            gpix > 0 ? 100.0 * gpix / (6555.5 / 2 / cli.channels * n) : 0.0, sh->plan[0]);
+            gpix > 0 ? 100.0 * gpix / (6555.5 / 2 / cli.channels * n) : 0.0, json_escape(sh->plan[0]).c_str());
     for (int k = 0; k < n; ++k) fprintf(f, "%s%.4f", k ? ", " : "", sh->loop_ms[k]);
     fprintf(f, "]}\n");
     fclose(f);

@@ -6,6 +6,7 @@ MPI+OpenMP and CUDA programs) on one C++/CUDA core:
   ``blur(img, reps, boundary=...)``        single GPU, torch tensors
   ``BlurPipeline``                         single GPU, stream of host images, copies overlapped
   ``parallel.ShardedBlur``                 one process per GPU, peer-memory halo exchange
+  ``parallel.ShardedPipeline``             stream of sharded images, PCIe copies overlapped with the loop
   ``parallel.LocalGrid``                   every rank in one process (tests, multi-GPU threads)
   ``reference_oracle`` / ``numpy_oracle``  CPU oracles
   ``rows_division`` / ``decompose`` / ``neighbours``   the reference's decomposition rule
@@ -16,7 +17,7 @@ from . import _lib
 from ._lib import B2CError
 from .ops import (BlurPipeline, Engine, blur, blur_file, clear_engine_cache, numpy_oracle, reference_oracle, sharded_oracle,
                   stencil_step)
-from .parallel import LocalGrid, ShardedBlur, block_of, decompose, neighbours, rows_division
+from .parallel import LocalGrid, ShardedBlur, ShardedPipeline, block_of, decompose, neighbours, rows_division
 from . import models, ops, parallel, utils
 
 __version__ = "0.1.0"

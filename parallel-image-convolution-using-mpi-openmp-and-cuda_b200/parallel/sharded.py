@@ -92,3 +92,76 @@ class ShardedBlur:
 
     def iterations_done(self) -> int:
         return self.engine.iterations_done()
+
+
+class ShardedPipeline:
+    """A stream of same-shaped sharded images through one :class:`ShardedBlur`.
+
+    Per image the work is unchanged — host->device copy of this rank's block from pinned memory,
+    initial halo exchange, ``repetitions`` iterations, device->host copy of the result — but the
+    PCIe copies run on two copy streams through device staging buffers, so the upload of image
+    i+1 and the download of image i-1 overlap the iterations of image i (the copy engines work
+    beside the SMs; PCIe is full duplex).  Only one stream ever carries the halo-exchanging
+    kernels, so no two kernels that wait on flags share a GPU.
+
+    No host barrier between images: a rank that runs ahead only writes frames that its
+    neighbours have finished reading (the last pass a rank completed required the neighbours'
+    flags of the pass before, exactly the slot-reuse rule of the iteration loop), and it cannot
+    start iterating before the neighbours' exchange of the same image has published its epoch.
+
+        pipe = ShardedPipeline(sharded, repetitions=1000)
+        for src, dst in zip(pinned_blocks_in, pinned_blocks_out):
+            pipe.submit(src, dst)          # every rank submits the same number of images
+        pipe.wait()
+    """
+
+    def __init__(self, sharded: ShardedBlur, repetitions: int, depth: int = 2):
+        if int(sharded.engine.opts.check_every):
+            raise ValueError("ShardedPipeline does not support check_every (the host must read the latch per image)")
+        self.sharded = sharded
+        self.repetitions = int(repetitions)
+        self.depth = int(depth)
+        dev = torch.device(f"cuda:{sharded.device}")
+        shape = sharded.block_shape
+        with torch.cuda.device(dev):
+            self._in = [torch.empty(shape, dtype=torch.uint8, device=dev) for _ in range(self.depth)]
+            self._out = [torch.empty(shape, dtype=torch.uint8, device=dev) for _ in range(self.depth)]
+            self.s_compute = torch.cuda.Stream(device=dev)
+            self.s_h2d = torch.cuda.Stream(device=dev)
+            self.s_d2h = torch.cuda.Stream(device=dev)
+            mk = lambda: [torch.cuda.Event() for _ in range(self.depth)]  # noqa: E731
+            self._in_ready, self._in_free, self._out_ready, self._out_free = mk(), mk(), mk(), mk()
+            torch.cuda.synchronize(dev)
+        if sharded.world > 1:
+            dist.barrier(group=sharded.group)   # once: every rank's engine is idle and mapped
+        self._n = 0
+
+    def submit(self, src: torch.Tensor, dst: torch.Tensor):
+        """Enqueue one image: ``src``/``dst`` are this rank's block (pinned CPU tensors). Returns at once."""
+        eng = self.sharded.engine
+        i = self._n % self.depth
+        first_use = self._n < self.depth
+        self._n += 1
+        with torch.cuda.device(self.sharded.device):
+            if not first_use:
+                self.s_h2d.wait_event(self._in_free[i])
+            with torch.cuda.stream(self.s_h2d):
+                self._in[i].copy_(src, non_blocking=True)
+                self._in_ready[i].record(self.s_h2d)
+            self.s_compute.wait_event(self._in_ready[i])
+            eng.load(self._in[i], stream=self.s_compute)
+            self._in_free[i].record(self.s_compute)
+            eng.exchange(stream=self.s_compute)
+            eng.run(self.repetitions, stream=self.s_compute)
+            if not first_use:
+                self.s_compute.wait_event(self._out_free[i])
+            eng.store(self._out[i], stream=self.s_compute)
+            self._out_ready[i].record(self.s_compute)
+            self.s_d2h.wait_event(self._out_ready[i])
+            with torch.cuda.stream(self.s_d2h):
+                dst.copy_(self._out[i], non_blocking=True)
+                self._out_free[i].record(self.s_d2h)
+
+    def wait(self):
+        for s in (self.s_h2d, self.s_compute, self.s_d2h):
+            s.synchronize()
