@@ -23,6 +23,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <new>
 #include <string>
 #include <vector>
 
@@ -46,7 +47,7 @@ struct Shared {
 double now_ms() {
     timespec ts;
     clock_gettime(CLOCK_MONOTONIC, &ts);
-    return ts.tv_sec * 1e3 + ts.tv_nsec * 1e-6;
+    return (double)ts.tv_sec * 1e3 + (double)ts.tv_nsec * 1e-6;
 }
 
 // Sense-reversing barrier over the shared mapping (the MPI_Barrier of :151).
@@ -272,13 +273,12 @@ int main(int argc, char **argv) {
         return EXIT_FAILURE;
     }
 
-    Shared *sh = static_cast<Shared *>(
-        mmap(nullptr, sizeof(Shared), PROT_READ | PROT_WRITE, MAP_SHARED | MAP_ANONYMOUS, -1, 0));
-    if (sh == MAP_FAILED) {
+    void *mem = mmap(nullptr, sizeof(Shared), PROT_READ | PROT_WRITE, MAP_SHARED | MAP_ANONYMOUS, -1, 0);
+    if (mem == MAP_FAILED) {
         perror("mmap");
         return EXIT_FAILURE;
     }
-    memset(sh, 0, sizeof *sh);
+    Shared *sh = new (mem) Shared();  // anonymous mappings start zeroed; this also starts the atomics' lifetime
 
     std::vector<pid_t> pids;
     for (int k = 0; k < n; ++k) {
