@@ -28,6 +28,7 @@ int parse_kernel(const char *s) {
     if (!strcmp(s, "naive")) return B2C_KERNEL_NAIVE;
     if (!strcmp(s, "stream")) return B2C_KERNEL_STREAM;
     if (!strcmp(s, "tma")) return B2C_KERNEL_TMA;
+    if (!strcmp(s, "resident")) return B2C_KERNEL_RESIDENT;
     return -1;
 }
 

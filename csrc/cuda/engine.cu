@@ -20,6 +20,7 @@
 #include "common.h"
 #include "kernels.h"
 #include "stencil_stream.cuh"
+#include "stencil_resident.h"
 #include "stencil_tma.h"
 
 #define CK(call)                                                                         \
@@ -107,6 +108,12 @@ struct b2c_engine {
     std::map<std::pair<int, int>, cudaGraphExec_t> graphs;
     NaiveWeights nw{};
     TmaState *tma = nullptr;
+    // resident kernel (B2C_KERNEL_RESIDENT): tile plan, exchange images, per-CTA epoch words
+    ResidentPlan res_plan{};
+    uint8_t *res_xbuf[2] = {nullptr, nullptr};
+    long long res_xpitch = 0;
+    uint32_t *res_flags = nullptr;   // sm_count x 32 words, then the error word
+    uint32_t res_epoch = 0;
     mutable BandPlan plan_cache[9];
     mutable bool plan_ok[9] = {false, false, false, false, false, false, false, false, false};
 };
@@ -351,7 +358,7 @@ void choose_plan(b2c_engine *e) {
     e->F = e->any_nb ? K : 1;
     if (e->kernel == B2C_KERNEL_NAIVE) e->F = 1;
     // the byte-per-thread kernel has no change detector: a check would always report "unchanged"
-    if (e->kernel == B2C_KERNEL_NAIVE) e->opts.check_every = 0;
+    if (e->kernel == B2C_KERNEL_NAIVE || e->kernel == B2C_KERNEL_RESIDENT) e->opts.check_every = 0;
 }
 
 // Rows per warp for large blocks are measured, not modelled: how the block scheduler packs
@@ -509,6 +516,41 @@ b2c_engine *b2c_engine_create(int device, int W, int H, int CH, int P, int Q, in
         b2c_engine_destroy(e);
         return nullptr;
     }
+    if (e->kernel == B2C_KERNEL_RESIDENT) {
+        int coop = 0;
+        cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, device);
+        // Exchange interval K (= halo depth): an explicit tb is rounded down to 4, 8 or 16 and falls
+        // back to a shorter interval when its halo does not fit; otherwise the K with the lowest
+        // modelled time wins.  Measured on B200 (profiles/tuning.md step 14): an iteration costs
+        // ~66.5 ns per row held by a warp, an exchange ~4 us whatever K is.
+        bool fits = false;
+        if (o.tb > 0) {
+            for (int k = o.tb >= 16 ? 16 : (o.tb >= 8 ? 8 : 4); k >= 4 && !fits; k >>= 1)
+                fits = resident_plan(e->bw, e->R, CH, k, e->sm_count, &e->res_plan);
+        } else {
+            double best = 1e300;
+            for (int k = 16; k >= 4; k >>= 1) {
+                ResidentPlan pl;
+                if (!resident_plan(e->bw, e->R, CH, k, e->sm_count, &pl)) continue;
+                const double us_per_iteration = pl.rw * 0.0665 + 4.0 / k;
+                if (us_per_iteration < best) { best = us_per_iteration; e->res_plan = pl; fits = true; }
+            }
+        }
+        if (P * Q != 1 || o.boundary == B2C_CUDA_COMPAT || !coop || !fits) {
+            set_error("the resident kernel needs one GPU, zero/torus, row bytes %% 8 == 0 and an image that fits "
+                      "the register files (%d x %d bytes does not, or cooperative launch is missing)", e->bw, e->R);
+            b2c_engine_destroy(e);
+            return nullptr;
+        }
+        e->res_xpitch = round_up(e->bw, 128);
+        const size_t xbytes = (size_t)(e->res_xpitch * e->R), fbytes = ((size_t)e->sm_count * 32 + 32) * sizeof(uint32_t);
+        if (cudaMalloc(&e->res_xbuf[0], xbytes) != cudaSuccess || cudaMalloc(&e->res_xbuf[1], xbytes) != cudaSuccess ||
+            cudaMalloc(&e->res_flags, fbytes) != cudaSuccess || cudaMemset(e->res_flags, 0, fbytes) != cudaSuccess) {
+            set_error("resident kernel buffers: %s", cudaGetErrorString(cudaGetLastError()));
+            b2c_engine_destroy(e);
+            return nullptr;
+        }
+    }
     if (e->kernel == B2C_KERNEL_TMA && o.boundary != B2C_CUDA_COMPAT) {
         e->tma = tma_create(e->alloc, e->pitch, e->R + 2 * kFrameRows, e->alloc_bytes);
         if (!e->tma) {
@@ -537,6 +579,8 @@ void b2c_engine_destroy(b2c_engine *e) {
     for (auto &g : e->graphs) cudaGraphExecDestroy(g.second);
     for (void *p : e->ipc_opened) cudaIpcCloseMemHandle(p);
     if (e->tma) tma_destroy(e->tma);
+    for (auto &b : e->res_xbuf) if (b) cudaFree(b);
+    if (e->res_flags) cudaFree(e->res_flags);
     for (auto &b : e->alloc) if (b) cudaFree(b);
     for (auto &b : e->cbuf) if (b) cudaFree(b);
     if (e->pad) cudaFree(e->pad);
@@ -753,6 +797,36 @@ int b2c_engine_run(b2c_engine *e, int reps, void *stream) {
         set_error("engine_run: call b2c_engine_exchange after upload on every rank first");
         return B2C_EINVAL;
     }
+    if (e->kernel == B2C_KERNEL_RESIDENT) {
+        // one cooperative launch for the whole run; CTAs trade rings through res_xbuf every 4 iterations
+        e->iters_done = reps;
+        if (reps == 0) return B2C_OK;
+        ResidentParams q{};
+        q.src = e->base[e->cur];
+        q.dst = e->base[e->cur ^ 1];
+        q.src_pitch = q.dst_pitch = e->pitch;
+        q.xbuf[0] = e->res_xbuf[0];
+        q.xbuf[1] = e->res_xbuf[1];
+        q.xpitch = e->res_xpitch;
+        q.flags = e->res_flags;
+        q.error = e->res_flags + (size_t)e->sm_count * 32;
+        q.epoch0 = e->res_epoch;
+        q.H = e->R;
+        q.bw = e->bw;
+        q.reps = reps;
+        q.strips = e->res_plan.strips;
+        q.ctarows = e->res_plan.ctarows;
+        q.torus = e->opts.boundary == B2C_TORUS;
+        {
+            const char *dbg = getenv("B200CONV_RES_DEBUG");   // profiling only, see stencil_resident.cu
+            q.debug = dbg ? atoi(dbg) : 0;
+        }
+        CK(launch_resident(e->res_plan, q, e->CH, s));
+        e->launches++;
+        e->res_epoch += (uint32_t)(ceil_div(reps, e->res_plan.k) - 1);
+        e->cur ^= 1;
+        return B2C_OK;
+    }
     const std::vector<Pass> passes = make_passes(e, reps);
     e->iters_done = reps;
     if (e->opts.check_every > 0) {
@@ -818,6 +892,14 @@ int b2c_engine_iterations_done(b2c_engine *e) {
     if (!e) return B2C_EINVAL;
     CK(cudaSetDevice(e->device));
     CK(cudaDeviceSynchronize());
+    if (e->res_flags) {
+        uint32_t err = 0;
+        CK(cudaMemcpy(&err, e->res_flags + (size_t)e->sm_count * 32, sizeof err, cudaMemcpyDeviceToHost));
+        if (err) {
+            set_error("resident kernel: a CTA waited too long for a neighbour's epoch");
+            return B2C_ECUDA;
+        }
+    }
     if (e->pending_converge_fixup) {
         e->pending_converge_fixup = false;
         uint32_t v[2] = {0, 0};
@@ -842,11 +924,24 @@ int b2c_engine_iterations_done(b2c_engine *e) {
 
 int64_t b2c_engine_launches(const b2c_engine *e) { return e ? e->launches : 0; }
 
+int b2c_resident_plan(int row_bytes, int rows, int channels, int k, int sms, int out[5]) {
+    ResidentPlan pl;
+    if (!resident_plan(row_bytes, rows, channels, k, sms, &pl)) return 0;
+    if (out) { out[0] = pl.rw; out[1] = pl.strips; out[2] = pl.ctarows; out[3] = pl.vr; out[4] = pl.vc; }
+    return 1;
+}
+
 int b2c_engine_describe(const b2c_engine *e, char *buf, size_t buflen) {
     if (!e || !buf) return B2C_EINVAL;
     const char *kn = e->kernel == B2C_KERNEL_NAIVE ? "naive" : (e->kernel == B2C_KERNEL_TMA ? "tma" : "stream");
     if (e->opts.boundary == B2C_CUDA_COMPAT) {
         snprintf(buf, buflen, "kernel=compat W=%d H=%d CH=%d", e->W, e->H, e->CH);
+        return B2C_OK;
+    }
+    if (e->kernel == B2C_KERNEL_RESIDENT) {
+        snprintf(buf, buflen, "kernel=resident tb=%d ctas=%dx%d rows_per_warp=%d valid=%dx%dB block=%dx%d(bytes %d)",
+                 e->res_plan.k, e->res_plan.ctarows, e->res_plan.strips, e->res_plan.rw, e->res_plan.vr, e->res_plan.vc, e->R, e->C,
+                 e->bw);
         return B2C_OK;
     }
     const BandPlan bp = make_band_plan(e, e->K);

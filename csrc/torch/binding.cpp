@@ -28,7 +28,8 @@ int kernel_code(const std::string &s) {
     if (s == "naive") return B2C_KERNEL_NAIVE;
     if (s == "stream") return B2C_KERNEL_STREAM;
     if (s == "tma") return B2C_KERNEL_TMA;
-    TORCH_CHECK(false, "kernel must be auto|naive|stream|tma, got ", s);
+    if (s == "resident") return B2C_KERNEL_RESIDENT;
+    TORCH_CHECK(false, "kernel must be auto|naive|stream|tma|resident, got ", s);
 }
 
 // blur(img[H,W] | img[H,W,3] uint8 CUDA, reps, boundary, filter, tb, kernel) -> Tensor

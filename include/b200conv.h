@@ -43,7 +43,10 @@ enum {
     B2C_KERNEL_AUTO = 0,   /* pick by shape                                    */
     B2C_KERNEL_NAIVE = 1,  /* one pass per iteration, byte-per-thread          */
     B2C_KERNEL_STREAM = 2, /* register-pipelined temporal blocking, LDG feed   */
-    B2C_KERNEL_TMA = 3     /* same pipeline fed by TMA bulk-tensor tiles       */
+    B2C_KERNEL_TMA = 3,    /* same pipeline fed by TMA bulk-tensor tiles       */
+    B2C_KERNEL_RESIDENT = 4 /* small images: whole image held in registers for the run
+                              (one GPU, gaussian, zero/torus, row bytes % 8 == 0;
+                              opt-in, never chosen by AUTO) */
 };
 
 /* Error codes (negative returns). */
@@ -219,6 +222,11 @@ int b2c_engine_run(b2c_engine *e, int repetitions, void *stream);
 int b2c_engine_iterations_done(b2c_engine *e);
 
 /* Kernel launches issued by this engine since creation. */
+/* Tile plan of the resident kernel (host only, no GPU needed): 1 and out = {rows per warp,
+ * strips, CTA rows, valid rows, valid bytes} when a row_bytes x rows image fits on `sms` SMs with
+ * an exchange every k (4, 8, 16) iterations, else 0. */
+int b2c_resident_plan(int row_bytes, int rows, int channels, int k, int sms, int out[5]);
+
 int64_t b2c_engine_launches(const b2c_engine *e);
 /* Human-readable plan (kernel, tb, strip, chunks, grid) for reports. */
 int b2c_engine_describe(const b2c_engine *e, char *buf, size_t buflen);

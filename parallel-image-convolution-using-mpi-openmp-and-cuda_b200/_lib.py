@@ -20,10 +20,11 @@ HANDLE_BYTES = 256
 
 ZERO, TORUS, CUDA_COMPAT = 0, 1, 2
 GAUSSIAN, BOX, EDGE = 0, 1, 2
-KERNEL_AUTO, KERNEL_NAIVE, KERNEL_STREAM, KERNEL_TMA = 0, 1, 2, 3
+KERNEL_AUTO, KERNEL_NAIVE, KERNEL_STREAM, KERNEL_TMA, KERNEL_RESIDENT = 0, 1, 2, 3, 4
 BOUNDARY = {"zero": ZERO, "torus": TORUS, "cuda-compat": CUDA_COMPAT, "cuda_compat": CUDA_COMPAT}
 FILTER = {"gaussian": GAUSSIAN, "box": BOX, "edge": EDGE}
-KERNEL = {"auto": KERNEL_AUTO, "naive": KERNEL_NAIVE, "stream": KERNEL_STREAM, "tma": KERNEL_TMA}
+KERNEL = {"auto": KERNEL_AUTO, "naive": KERNEL_NAIVE, "stream": KERNEL_STREAM, "tma": KERNEL_TMA,
+          "resident": KERNEL_RESIDENT}
 DIRS = ("N", "S", "W", "E", "NW", "NE", "SW", "SE")
 
 
@@ -91,6 +92,7 @@ def _load() -> C.CDLL:
         "b2c_engine_run": (I, [P, I, V]),
         "b2c_engine_iterations_done": (I, [P]),
         "b2c_engine_launches": (L, [P]),
+        "b2c_resident_plan": (I, [I, I, I, I, I, C.POINTER(I)]),
         "b2c_engine_describe": (I, [P, C.c_char_p, C.c_size_t]),
         "b2c_engine_set_delay": (I, [P, L]),
         "b2c_blur_device": (I, [u8p, L, u8p, L, I, I, I, I, C.POINTER(Opts), V]),
