@@ -10,10 +10,9 @@ from __future__ import annotations
 import ctypes as C
 from collections import OrderedDict
 
-import numpy as np
 import torch
 
-from .._lib import HANDLE_BYTES, B2CError, Opts, check, last_error, lib, make_opts
+from .._lib import HANDLE_BYTES, B2CError, check, last_error, lib, make_opts
 
 
 def _stream_ptr(stream=None) -> int:

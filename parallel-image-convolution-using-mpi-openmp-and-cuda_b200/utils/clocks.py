@@ -4,7 +4,6 @@ from __future__ import annotations
 import statistics
 import subprocess
 import threading
-import time
 
 _Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
       "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"

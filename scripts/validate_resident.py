@@ -15,7 +15,6 @@ import torch
 
 ROOT = Path(__file__).resolve().parent.parent
 sys.path.insert(0, str(ROOT))
-import b200conv  # noqa: E402
 from b200conv import Engine, blur, reference_oracle  # noqa: E402
 
 

@@ -1,6 +1,5 @@
 """T3 on real GPUs: one process per GPU (torch.distributed + NCCL for plumbing only), halos
 through cudaIpc peer mappings.  Skipped on boxes with fewer than two GPUs."""
-import os
 import socket
 import subprocess
 import sys

@@ -8,7 +8,6 @@ before the parity fix) must be caught as a deadlock.
 """
 import shutil
 import subprocess
-import sys
 from pathlib import Path
 
 import numpy as np

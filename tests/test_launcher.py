@@ -1,9 +1,7 @@
 """The native launcher `lib/b200conv`: reference CLI parity (usage text, exit status, output
 name) on CPU, whole-program runs on GPU."""
 import json
-import os
 import subprocess
-from pathlib import Path
 
 import numpy as np
 import pytest
