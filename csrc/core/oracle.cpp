@@ -12,6 +12,7 @@
 //   * b2c_oracle_blur_sharded: host emulation of the engine's frame/epoch halo
 //     protocol on a P x Q grid (tests decomposition independence without GPUs).
 #include <algorithm>
+#include <thread>
 #include <vector>
 
 #include "common.h"
@@ -164,6 +165,39 @@ int b2c_oracle_blur(const uint8_t *in, uint8_t *out, int W, int H, int ch, int r
         return B2C_OK;
     }
     blur_padded(in, out, W, H, ch, reps, boundary == B2C_TORUS, w);
+    return B2C_OK;
+}
+
+// One iteration on caller-framed host memory, rows split statically over `threads` threads: the
+// CPU counterpart of b2c_stencil_step_device, and — with ranks exchanging the frame over
+// torch.distributed/gloo (parallel/sendrecv.py) — this repo's analogue of the reference's MPI and
+// MPI+OpenMP programs (Convolution(), mpi_convolution.c:288-299; the static row schedule of
+// omp_convolution.c:292,297).
+int b2c_stencil_step_host(const uint8_t *src, uint8_t *dst, int64_t pitch, int rows, int row_bytes, int ch,
+                          int filter, int threads) {
+    if (!src || !dst || src == dst || rows <= 0 || row_bytes <= 0 || (ch != 1 && ch != 3) ||
+        pitch < row_bytes + 2 * ch || filter < B2C_GAUSSIAN || filter > B2C_EDGE) {
+        b2c::set_error("stencil_step_host: bad arguments");
+        return B2C_EINVAL;
+    }
+    const Weights w = make_weights(filter);
+    auto band = [&](int r0, int r1) {
+        for (int r = r0; r < r1; ++r) {
+            const uint8_t *s = src + (int64_t)r * pitch;
+            uint8_t *d = dst + (int64_t)r * pitch;
+            for (int x = 0; x < row_bytes; ++x) d[x] = tap9(s + x, pitch, ch, w);
+        }
+    };
+    int nt = threads > 0 ? threads : (int)std::thread::hardware_concurrency();
+    nt = std::max(1, std::min(nt, std::min(rows, 64)));
+    if (nt == 1) {
+        band(0, rows);
+        return B2C_OK;
+    }
+    std::vector<std::thread> pool;
+    for (int t = 0; t < nt; ++t)
+        pool.emplace_back(band, (int)((int64_t)rows * t / nt), (int)((int64_t)rows * (t + 1) / nt));
+    for (auto &t : pool) t.join();
     return B2C_OK;
 }
 

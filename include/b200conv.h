@@ -158,6 +158,15 @@ int b2c_emulate_halo_threads(const uint8_t *in, uint8_t *out, int width, int hei
                              int repetitions, int boundary, int grid_rows, int grid_cols,
                              const b2c_emul_opts *opts, int *iterations_done);
 
+/* One plain iteration on caller-framed HOST memory (`src`/`dst` point at the
+ * interior origin; one halo row above/below and `channels` halo bytes left/right
+ * must exist), rows split over `threads` threads (0 = all cores).  With the
+ * frame exchanged between processes over torch.distributed/gloo this is the CPU
+ * arm of the package (what mpi_convolution.c / omp_convolution.c are to the
+ * reference); the GPU twin is b2c_stencil_step_device. */
+int b2c_stencil_step_host(const uint8_t *src, uint8_t *dst, int64_t pitch, int rows, int row_bytes,
+                          int channels, int filter, int threads);
+
 /* --------------------------------------------------------------- GPU engine */
 
 typedef struct b2c_opts {

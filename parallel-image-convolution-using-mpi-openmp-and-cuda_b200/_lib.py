@@ -76,6 +76,7 @@ def _load() -> C.CDLL:
         "b2c_oracle_blur": (I, [u8p, u8p, I, I, I, I, I, I]),
         "b2c_oracle_blur_sharded": (I, [u8p, u8p, I, I, I, I, I, I, I, I]),
         "b2c_emulate_halo_threads": (I, [u8p, u8p, I, I, I, I, I, I, I, C.POINTER(EmulOpts), C.POINTER(I)]),
+        "b2c_stencil_step_host": (I, [u8p, u8p, L, I, I, I, I, I]),
         "b2c_default_opts": (None, [C.POINTER(Opts)]),
         "b2c_engine_create": (P, [I, I, I, I, I, I, I, C.POINTER(Opts)]),
         "b2c_engine_destroy": (None, [P]),

@@ -223,8 +223,9 @@ class BlurPipeline:
 
 
 def stencil_step(src: torch.Tensor, dst: torch.Tensor, rows: int, row_bytes: int, channels: int,
-                 filter: str = "gaussian"):
-    """One plain iteration on caller-framed CUDA buffers (see ``b2c_stencil_step_device``).
+                 filter: str = "gaussian", threads: int = 0):
+    """One plain iteration on caller-framed buffers, CUDA (``b2c_stencil_step_device``, current
+    stream) or CPU (``b2c_stencil_step_host``, ``threads`` threads, 0 = all cores).
 
     ``src``/``dst``: uint8 ``[rows+2, pitch]`` with the block at ``[1:rows+1, channels:channels+row_bytes]``.
     """
@@ -232,8 +233,12 @@ def stencil_step(src: torch.Tensor, dst: torch.Tensor, rows: int, row_bytes: int
 
     pitch = src.stride(0)
     off = pitch + channels
-    check(lib.b2c_stencil_step_device(src.data_ptr() + off, dst.data_ptr() + off, pitch, int(rows), int(row_bytes),
-                                      int(channels), FILTER[filter], _stream_ptr()), "stencil_step")
+    if src.is_cuda:
+        check(lib.b2c_stencil_step_device(src.data_ptr() + off, dst.data_ptr() + off, pitch, int(rows), int(row_bytes),
+                                          int(channels), FILTER[filter], _stream_ptr()), "stencil_step")
+    else:
+        check(lib.b2c_stencil_step_host(src.data_ptr() + off, dst.data_ptr() + off, pitch, int(rows), int(row_bytes),
+                                        int(channels), FILTER[filter], int(threads)), "stencil_step")
 
 
 def load_torch_ops():

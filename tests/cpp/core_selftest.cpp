@@ -168,6 +168,27 @@ static void test_oracles() {
     EXPECT(b2c_oracle_blur(a.data(), a.data(), 24, 24, 3, 4, B2C_ZERO, B2C_GAUSSIAN) == B2C_OK && a == want);
 }
 
+static void test_host_step() {
+    for (int ch : {1, 3})
+        for (int filter : {B2C_GAUSSIAN, B2C_BOX, B2C_EDGE})
+            for (int threads : {1, 3, 0}) {
+                const int W = 21, H = 13;
+                const int64_t bw = (int64_t)W * ch, pitch = bw + 2 * ch + 3;
+                const std::vector<uint8_t> in = noise((size_t)(bw * H), 11);
+                std::vector<uint8_t> src((size_t)(pitch * (H + 2)), 0), dst(src.size(), 0x5A), want(in.size());
+                for (int r = 0; r < H; ++r) memcpy(&src[(size_t)((r + 1) * pitch + ch)], &in[(size_t)(r * bw)], (size_t)bw);
+                EXPECT(b2c_stencil_step_host(&src[(size_t)(pitch + ch)], &dst[(size_t)(pitch + ch)], pitch, H, (int)bw, ch, filter,
+                                             threads) == B2C_OK);
+                EXPECT(b2c_oracle_blur(in.data(), want.data(), W, H, ch, 1, B2C_ZERO, filter) == B2C_OK);
+                for (int r = 0; r < H; ++r)
+                    EXPECT(!memcmp(&dst[(size_t)((r + 1) * pitch + ch)], &want[(size_t)(r * bw)], (size_t)bw));
+                EXPECT(dst[0] == 0x5A && dst[(size_t)(pitch + ch - 1)] == 0x5A);   // frame untouched
+            }
+    std::vector<uint8_t> a(64, 0);
+    EXPECT(b2c_stencil_step_host(a.data(), a.data(), 8, 2, 4, 1, B2C_GAUSSIAN, 1) == B2C_EINVAL);   // in place
+    EXPECT(b2c_stencil_step_host(a.data(), a.data() + 32, 4, 2, 4, 1, B2C_GAUSSIAN, 1) == B2C_EINVAL);   // pitch too small
+}
+
 static void test_host_models() {
     const int W = 24, H = 24;
     for (int ch : {1, 3})
@@ -199,6 +220,7 @@ int main(int argc, char **argv) {
     test_cli();
     test_rawio(dir);
     test_oracles();
+    test_host_step();
     test_host_models();
     printf("core_selftest: %d failure(s)\n", g_fail);
     return g_fail ? 1 : 0;
