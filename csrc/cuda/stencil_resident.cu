@@ -13,12 +13,14 @@
 //     — instruction-level parallelism instead of a dependent chain — done in place;
 //   * inside a CTA neighbouring warps trade the horizontal sums of their first and last row through
 //     shared memory, one __syncthreads per iteration (double-buffered by iteration parity);
-//   * between CTAs the window carries a halo of K = 4 rows and K*CH bytes (rounded to the lane
-//     width) that is recomputed redundantly; every K iterations each CTA writes the K-deep ring of
-//     its valid region to an exchange image in L2 (one per epoch parity), publishes an epoch with
-//     st.release.gpu, waits for its (up to) 8 neighbours with ld.acquire.gpu and reloads its halo.
+//   * between CTAs the window carries a halo of K rows and K*CH bytes (rounded to the lane width;
+//     K = 4, 8 or 16, chosen per shape by the engine) that is recomputed redundantly; every K
+//     iterations each CTA writes the K-deep ring of its valid region to an exchange image in L2 (one
+//     per epoch parity), publishes an epoch with st.release.gpu, waits for its (up to) 8 neighbours
+//     with ld.acquire.gpu and reloads its halo with predicated loads issued back to back.
 //     Same slot-reuse argument as the multi-GPU protocol: a CTA can write epoch e+2 only after it
 //     has seen its neighbours' epoch e+1, which they publish after reading epoch e.
+//     Measured: an iteration costs ~66 ns per row held by a warp, an exchange ~4 us.
 //   * ZERO boundary: cells outside the image are forced to zero by the mask / byte-permute that
 //     does the >>4 anyway (no extra instruction); TORUS: halo loads wrap around the image.
 //
