@@ -40,7 +40,6 @@ struct Rank {
     std::atomic<uint32_t> flag[8];
     std::unique_ptr<std::atomic<uint32_t>[]> slots;  // 2 sets x n ranks
     int iters = 0;
-    int final_buf = 0;
 };
 
 struct Pass {
@@ -113,7 +112,7 @@ struct World {
             if (me.nb[d] >= 0) ranks[me.nb[d]].flag[b2c::opposite_dir(d)].store(epoch, std::memory_order_release);
     }
 
-    void run_rank(int q, const uint8_t *in) {
+    void run_rank(int q, const uint8_t *in, uint8_t *out) {
         Rank &me = ranks[q];
         std::mt19937 rng(o.seed * 7919u + (unsigned)q);
         auto jitter = [&] {
@@ -123,23 +122,32 @@ struct World {
         const int r0 = (q / Q) * R, c0 = (q % Q) * C;
         const int64_t c0b = (int64_t)(q % Q) * bw;
 
-        // "upload": the whole framed buffer is rewritten, so nobody may push before everyone is here
-        for (auto &b : me.buf) b.assign((size_t)(pitch * rows), 0);
-        for (int r = 0; r < R; ++r)
-            memcpy(&me.buf[0][(r + F) * pitch + fb], in + ((int64_t)(r0 + r) * W + c0) * ch, (size_t)bw);
-        arrived.fetch_add(1, std::memory_order_acq_rel);
-        if (!wait_for([&] { return arrived.load(std::memory_order_acquire) >= n; })) return;
-
-        // initial exchange = epoch 1
-        jitter();
-        push_ring(q, 0);
-        publish(q, 1);
-        uint32_t epoch = 1;
+        uint32_t epoch = 0;
         int cur = 0;
         uint32_t seq = 0;
         bool converged = false;
         std::vector<uint8_t> t0, t1;
         me.iters = passes.empty() ? 0 : passes.back().iters_after;
+        const int nimg = std::max(1, o.images);
+        // allocation: the whole framed buffers are written, so nobody may push before everyone is here
+        for (auto &b : me.buf) b.assign((size_t)(pitch * rows), 0);
+        arrived.fetch_add(1, std::memory_order_acq_rel);
+        if (!wait_for([&] { return arrived.load(std::memory_order_acquire) >= n; })) return;
+
+        for (int img = 0; img < nimg; ++img) {
+        // "upload" of image `img` (= the input with every byte XORed by 37*img): interior of the
+        // current buffer only, like the engine's 2-D copy.  From the second image on there is NO
+        // barrier (ShardedPipeline): neighbours may still be in the last pass of the previous image.
+        for (int r = 0; r < R; ++r) {
+            uint8_t *d = &me.buf[cur][(r + F) * pitch + fb];
+            const uint8_t *s = in + ((int64_t)(r0 + r) * W + c0) * ch;
+            for (int64_t x = 0; x < bw; ++x) d[x] = (uint8_t)(s[x] ^ (uint8_t)(37 * img));
+        }
+        // initial exchange of this image: push, publish, no wait (b2c_engine_exchange)
+        jitter();
+        push_ring(q, cur);
+        publish(q, epoch + 1);
+        epoch++;
 
         for (const Pass &ps : passes) {
             unsigned changed = 0;
@@ -196,7 +204,11 @@ struct World {
                 }
             }
         }
-        me.final_buf = cur;
+        // "download": this rank's block of result `img`
+        for (int r = 0; r < R; ++r)
+            memcpy(out + (int64_t)img * W * H * ch + ((int64_t)(r0 + r) * W + c0) * ch, &me.buf[cur][(r + F) * pitch + fb],
+                   (size_t)bw);
+        }   // images
     }
 };
 
@@ -205,7 +217,8 @@ struct World {
 extern "C" int b2c_emulate_halo_threads(const uint8_t *in, uint8_t *out, int W, int H, int ch, int reps, int boundary,
                                         int P, int Q, const b2c_emul_opts *opts, int *iterations_done) {
     if (!in || !out || !opts || W <= 0 || H <= 0 || (ch != 1 && ch != 3) || reps < 0 || P <= 0 || Q <= 0 || H % P ||
-        W % Q || P * Q > 64 || (boundary != B2C_ZERO && boundary != B2C_TORUS)) {
+        W % Q || P * Q > 64 || (boundary != B2C_ZERO && boundary != B2C_TORUS) ||
+        (opts->images > 1 && opts->check_every > 0)) {
         b2c::set_error("emulate_halo_threads: bad arguments");
         return B2C_EINVAL;
     }
@@ -229,21 +242,17 @@ extern "C" int b2c_emulate_halo_threads(const uint8_t *in, uint8_t *out, int W, 
     }
     w.deadline = Clock::now() + std::chrono::milliseconds(opts->timeout_ms > 0 ? opts->timeout_ms : 20000);
     std::vector<std::thread> th;
-    for (int q = 0; q < w.n; ++q) th.emplace_back([&w, q, in] { w.run_rank(q, in); });
+    for (int q = 0; q < w.n; ++q) th.emplace_back([&w, q, in, out] { w.run_rank(q, in, out); });
     for (auto &t : th) t.join();
     if (w.failed.load()) {
         b2c::set_error("emulate_halo_threads: a rank waited past the deadline (protocol deadlock)");
         return B2C_ETIMEOUT;
     }
-    for (int q = 0; q < w.n; ++q) {
-        const int r0 = (q / Q) * w.R, c0 = (q % Q) * w.C;
-        for (int r = 0; r < w.R; ++r)
-            memcpy(out + ((int64_t)(r0 + r) * W + c0) * ch, &w.ranks[q].buf[w.ranks[q].final_buf][(r + w.F) * w.pitch + w.fb], (size_t)w.bw);
+    for (int q = 0; q < w.n; ++q)
         if (w.ranks[q].iters != w.ranks[0].iters) {
             b2c::set_error("emulate_halo_threads: ranks disagree on the iteration count");
             return B2C_EINVAL;
         }
-    }
     if (iterations_done) *iterations_done = w.ranks[0].iters;
     return B2C_OK;
 }

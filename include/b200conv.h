@@ -150,9 +150,12 @@ typedef struct b2c_emul_opts {
     int single_slot_set; /* 1 = model one convergence slot set instead of two (regression) */
     int stall_rank;      /* this rank sleeps stall_ms between publishing and reading its    */
     int stall_ms;        /*   convergence slots; -1 / 0 = nobody                            */
+    int images;          /* > 1: that many images back to back through the same buffers with no */
+                         /*   barrier in between (image j = input XOR 37*j); needs check_every 0 */
 } b2c_emul_opts;
 
-/* Returns B2C_OK (out = gathered image, *iterations_done = iterations run),
+/* Returns B2C_OK (out = the gathered result of every image, max(1, images) x H x W*CH bytes;
+ * *iterations_done = iterations run per image),
  * B2C_EINVAL, or B2C_ETIMEOUT when a rank waited past the deadline. */
 int b2c_emulate_halo_threads(const uint8_t *in, uint8_t *out, int width, int height, int channels,
                              int repetitions, int boundary, int grid_rows, int grid_cols,

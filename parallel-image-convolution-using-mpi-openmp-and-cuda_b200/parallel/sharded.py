@@ -108,6 +108,8 @@ class ShardedPipeline:
     neighbours have finished reading (the last pass a rank completed required the neighbours'
     flags of the pass before, exactly the slot-reuse rule of the iteration loop), and it cannot
     start iterating before the neighbours' exchange of the same image has published its epoch.
+    The threaded host model runs exactly this (``images`` > 1, csrc/core/halo_emul.cpp) with skewed
+    ranks, under ThreadSanitizer too (tests/test_halo_model.py).
 
         pipe = ShardedPipeline(sharded, repetitions=1000)
         for src, dst in zip(pinned_blocks_in, pinned_blocks_out):

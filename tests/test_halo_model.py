@@ -41,6 +41,18 @@ def test_many_epochs_with_skewed_ranks():
     assert iters == 500 and (out == reference_oracle(img, 500, "torus")).all()
 
 
+@pytest.mark.parametrize("grid,boundary,reps", [((2, 2), "zero", 9), ((1, 4), "torus", 9), ((2, 4), "torus", 12),
+                                                ((4, 2), "zero", 5), ((1, 2), "torus", 1)])
+def test_images_back_to_back_without_a_barrier(grid, boundary, reps):
+    # the ShardedPipeline claim: a rank may upload and exchange the next image while its neighbours
+    # are still in the last pass of the previous one (odd pass counts flip the buffer parity per image)
+    img = rnd(16, 32, 3, seed=7)
+    outs, iters = threaded_halo_model(img, reps, grid, boundary, tb=4, max_delay_us=300, seed=11, images=4)
+    assert iters == reps
+    for j, out in enumerate(outs):
+        assert (out == reference_oracle(img ^ np.uint8((37 * j) & 255), reps, boundary)).all(), j
+
+
 def test_halo_depth_is_clamped_to_the_block():
     img = rnd(4, 8, 1, seed=3)                      # 2x2 blocks on a 2x4 grid: tb=8 must clamp to 2
     out, _ = threaded_halo_model(img, 9, (2, 4), "torus", tb=8)
@@ -90,6 +102,18 @@ int main() {
             int iters = 0;
             int rc = b2c_emulate_halo_threads(in.data(), got.data(), W, H, ch, reps, boundary, 2, 4, &o, &iters);
             bad += rc != B2C_OK || memcmp(want.data(), got.data(), got.size()) != 0;
+            {   // four images back to back with no barrier in between (ShardedPipeline)
+                b2c_emul_opts p = o;
+                p.images = 4;
+                std::vector<uint8_t> many(in.size() * 4), x(in.size());
+                rc = b2c_emulate_halo_threads(in.data(), many.data(), W, H, ch, 9, boundary, 2, 4, &p, &iters);
+                bad += rc != B2C_OK;
+                for (int j = 0; j < 4; ++j) {
+                    for (size_t i = 0; i < in.size(); ++i) x[i] = (uint8_t)(in[i] ^ (uint8_t)(37 * j));
+                    b2c_oracle_blur(x.data(), want.data(), W, H, ch, 9, boundary, B2C_GAUSSIAN);
+                    bad += memcmp(want.data(), many.data() + (size_t)j * in.size(), in.size()) != 0;
+                }
+            }
             o.check_every = 4;   // convergence exchange under the race detector as well
             rc = b2c_emulate_halo_threads(in.data(), got.data(), W, H, ch, 400, boundary, 2, 2, &o, &iters);
             b2c_oracle_blur(in.data(), want.data(), W, H, ch, iters, boundary, B2C_GAUSSIAN);
