@@ -924,13 +924,6 @@ int b2c_engine_iterations_done(b2c_engine *e) {
 
 int64_t b2c_engine_launches(const b2c_engine *e) { return e ? e->launches : 0; }
 
-int b2c_resident_plan(int row_bytes, int rows, int channels, int k, int sms, int out[5]) {
-    ResidentPlan pl;
-    if (!resident_plan(row_bytes, rows, channels, k, sms, &pl)) return 0;
-    if (out) { out[0] = pl.rw; out[1] = pl.strips; out[2] = pl.ctarows; out[3] = pl.vr; out[4] = pl.vc; }
-    return 1;
-}
-
 int b2c_engine_describe(const b2c_engine *e, char *buf, size_t buflen) {
     if (!e || !buf) return B2C_EINVAL;
     const char *kn = e->kernel == B2C_KERNEL_NAIVE ? "naive" : (e->kernel == B2C_KERNEL_TMA ? "tma" : "stream");

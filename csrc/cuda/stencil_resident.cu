@@ -37,15 +37,7 @@
 namespace b2c {
 namespace {
 
-constexpr int kResWarps = 16;               // warps per CTA (one CTA per SM)
-constexpr int kResNW = 2;                   // 32-bit words per lane per row
-constexpr int kResSB = kResNW * 4;          // bytes per lane per row
-constexpr int kResWinB = 32 * kResSB;       // window width in bytes
 constexpr long long kResTimeout = 3ll << 30;  // clocks (~1.6 s) before a wait gives up
-
-// K = iterations between two inter-CTA exchanges = halo depth in rows; the halo is K*CH bytes wide,
-// rounded up to whole lanes.
-constexpr int res_halo_bytes(int ch, int k) { return (k * ch + kResSB - 1) / kResSB * kResSB; }
 
 __device__ __forceinline__ uint32_t ld_acquire_gpu(const uint32_t *p) {
     uint32_t v;
@@ -310,25 +302,6 @@ cudaError_t launch_rw(const ResidentParams &p, int ch, int k, int ctas, cudaStre
 }
 
 }  // namespace
-
-bool resident_plan(int bw, int H, int ch, int k, int sms, ResidentPlan *out) {
-    if (k != 4 && k != 8 && k != 16) return false;
-    const int HB = res_halo_bytes(ch, k), VC = kResWinB - 2 * HB;
-    if (bw <= 0 || H < k || bw < HB || bw % kResSB != 0) return false;
-    const int strips = (int)ceil_div(bw, VC);
-    if (bw - (strips - 1) * VC < HB) return false;   // a halo must come from one neighbour only
-    static const int cand[] = {4, 6, 8, 10, 12, 14, 16};
-    for (int rw : cand) {
-        const int VR = kResWarps * rw - 2 * k;
-        if (VR < k) continue;
-        const int ctarows = (int)ceil_div(H, VR);
-        if (H - (ctarows - 1) * VR < k) continue;
-        if ((long long)strips * ctarows > sms) continue;
-        if (out) *out = ResidentPlan{rw, k, strips, ctarows, VR, VC};
-        return true;
-    }
-    return false;
-}
 
 cudaError_t launch_resident(const ResidentPlan &plan, const ResidentParams &p, int ch, cudaStream_t s) {
     const int ctas = plan.strips * plan.ctarows;

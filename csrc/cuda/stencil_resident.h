@@ -6,15 +6,9 @@
 
 #include <cstdint>
 
-namespace b2c {
+#include "resident_plan.h"
 
-struct ResidentPlan {
-    int rw;        // rows per warp (template instance)
-    int k;         // iterations between two exchanges = halo depth (4, 8 or 16)
-    int strips;    // CTA columns
-    int ctarows;   // CTA rows
-    int vr, vc;    // valid rows / bytes per CTA
-};
+namespace b2c {
 
 struct ResidentParams {
     const uint8_t *src;   // image origin (8-byte aligned)
@@ -31,10 +25,6 @@ struct ResidentParams {
     int torus;
     int debug;            // profiling switches, 0 in production (see the kernel)
 };
-
-// Smallest tile that covers a bw x H byte image with at most `sms` CTAs; false when the image is
-// too large (or too awkward: bw must be a multiple of 8) for the resident kernel.
-bool resident_plan(int bw, int H, int ch, int k, int sms, ResidentPlan *out);
 
 cudaError_t launch_resident(const ResidentPlan &plan, const ResidentParams &p, int ch, cudaStream_t s);
 

@@ -170,6 +170,14 @@ int b2c_emulate_halo_threads(const uint8_t *in, uint8_t *out, int width, int hei
 int b2c_stencil_step_host(const uint8_t *src, uint8_t *dst, int64_t pitch, int rows, int row_bytes,
                           int channels, int filter, int threads);
 
+/* Threaded host model of the resident kernel's CTA protocol (one thread per CTA, private window,
+ * shared exchange images by epoch parity, release/acquire epoch flags): out = blurred image.
+ * k = exchange interval (4, 8, 16), sms = CTA budget.  B2C_EINVAL when the image does not fit the
+ * tile plan, B2C_ETIMEOUT on a deadlock.  No counterpart in the reference. */
+int b2c_emulate_resident_threads(const uint8_t *in, uint8_t *out, int width, int height, int channels,
+                                 int repetitions, int boundary, int k, int sms, int max_delay_us,
+                                 unsigned seed);
+
 /* --------------------------------------------------------------- GPU engine */
 
 typedef struct b2c_opts {

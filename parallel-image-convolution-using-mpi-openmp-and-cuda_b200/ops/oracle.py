@@ -6,6 +6,7 @@
                         cross-check the C++ oracle (mpi/mpi_convolution.c:301-322 semantics at
                         one rank; torus per README.md:63-66).
 ``sharded_oracle``    — host emulation of the multi-rank frame/epoch halo protocol.
+``threaded_resident_model`` — one thread per CTA of the resident kernel (tile plan, ring/halo exchange images, epochs).
 ``threaded_halo_model`` — the same protocol with one thread per rank, atomics for the epoch flags
                         and the convergence slots, and injected delays (csrc/core/halo_emul.cpp).
 """
@@ -74,6 +75,16 @@ def threaded_halo_model(img, reps: int, grid, boundary: str = "zero", tb: int = 
     if n == 1:
         return restore(out[0]), iters.value
     return [restore(out[j]) for j in range(n)], iters.value
+
+
+def threaded_resident_model(img, reps: int, boundary: str = "zero", k: int = 4, sms: int = 148,
+                            max_delay_us: int = 0, seed: int = 0):
+    """Host model of the resident kernel's CTA protocol (csrc/core/resident_emul.cpp): one thread per CTA."""
+    flat, w, h, ch, restore = _as_image(img)
+    out = np.empty_like(flat)
+    check(lib.b2c_emulate_resident_threads(flat.ctypes.data, out.ctypes.data, w, h, ch, int(reps), BOUNDARY[boundary],
+                                           int(k), int(sms), int(max_delay_us), int(seed)), "emulate_resident_threads")
+    return restore(out)
 
 
 def numpy_oracle(img, reps: int, boundary: str = "zero"):

@@ -211,7 +211,16 @@ static void test_host_models() {
                     EXPECT(iters == reps && got == want);
                 }
             EXPECT(b2c_oracle_blur_sharded(in.data(), got.data(), W, H, ch, 3, boundary, 5, 1, 1) == B2C_EINVAL);  // 24 % 5
+            // resident kernel: tile planner and the CTA protocol model (24 x 24 pixels = one tile)
+            EXPECT(b2c_oracle_blur(in.data(), want.data(), W, H, ch, 11, boundary, B2C_GAUSSIAN) == B2C_OK);
+            EXPECT(b2c_emulate_resident_threads(in.data(), got.data(), W, H, ch, 11, boundary, 4, 148, 0, 1) == B2C_OK);
+            EXPECT(got == want);
+            EXPECT(b2c_emulate_resident_threads(in.data(), got.data(), W, H, ch, 11, boundary, 5, 148, 0, 1) == B2C_EINVAL);
         }
+    int pl[5];
+    EXPECT(b2c_resident_plan(1920, 2520, 1, 8, 148, pl) == 1 && pl[0] == 10 && pl[1] == 8 && pl[2] == 18);
+    EXPECT(b2c_resident_plan(1924, 2520, 1, 8, 148, pl) == 0);
+    EXPECT(b2c_resident_plan(16384, 16384, 1, 4, 148, nullptr) == 0);
 }
 
 int main(int argc, char **argv) {

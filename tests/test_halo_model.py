@@ -14,7 +14,7 @@ import numpy as np
 import pytest
 
 from b200conv import B2CError, reference_oracle
-from b200conv.ops import threaded_halo_model
+from b200conv.ops import threaded_halo_model, threaded_resident_model
 
 ROOT = Path(__file__).resolve().parent.parent
 
@@ -81,6 +81,19 @@ def test_single_slot_set_loses_a_tag_and_two_sets_do_not():
     assert iters == 16 and (out == reference_oracle(img, 16, "torus")).all()
 
 
+@pytest.mark.parametrize("case", [
+    (40, 64, 1, 9, "torus", 4, 148), (130, 488, 1, 13, "zero", 4, 148), (200, 96, 3, 19, "torus", 8, 148),
+    (300, 520, 1, 6, "torus", 4, 12), (90, 304, 1, 33, "zero", 16, 148), (61, 8, 1, 7, "torus", 4, 148),
+])
+def test_resident_cta_protocol_model(case):
+    # one thread per CTA of the resident kernel: private window, ring out / halo in through two
+    # exchange images chosen by epoch parity, epoch flags, CTAs skewed by random sleeps
+    h, w, ch, reps, boundary, k, sms = case
+    img = rnd(h, w, ch, seed=8)
+    got = threaded_resident_model(img, reps, boundary, k=k, sms=sms, max_delay_us=200, seed=3)
+    assert (got == reference_oracle(img, reps, boundary)).all()
+
+
 TSAN_MAIN = r"""
 #include <cstdio>
 #include <cstdlib>
@@ -119,6 +132,15 @@ int main() {
             b2c_oracle_blur(in.data(), want.data(), W, H, ch, iters, boundary, B2C_GAUSSIAN);
             bad += rc != B2C_OK || memcmp(want.data(), got.data(), got.size()) != 0;
         }
+    for (int boundary = 0; boundary <= 1; ++boundary) {   // CTA protocol of the resident kernel, 3 x 3 tiles
+        const int RW_ = 488, RH_ = 130, reps2 = 13;
+        std::vector<uint8_t> in((size_t)RW_ * RH_), want(in.size()), got(in.size());
+        srand(9);
+        for (auto &b : in) b = (uint8_t)rand();
+        b2c_oracle_blur(in.data(), want.data(), RW_, RH_, 1, reps2, boundary, B2C_GAUSSIAN);
+        int rc = b2c_emulate_resident_threads(in.data(), got.data(), RW_, RH_, 1, reps2, boundary, 4, 148, 100, 5);
+        bad += rc != B2C_OK || memcmp(want.data(), got.data(), got.size()) != 0;
+    }
     printf("bad=%d\n", bad);
     return bad != 0;
 }
@@ -130,7 +152,7 @@ def test_model_is_race_free_under_thread_sanitizer(tmp_path):
     main = tmp_path / "main.cpp"
     main.write_text(TSAN_MAIN)
     exe = tmp_path / "halo_tsan"
-    srcs = [str(ROOT / "csrc/core" / f) for f in ("halo_emul.cpp", "oracle.cpp", "decomp.cpp")]
+    srcs = [str(ROOT / "csrc/core" / f) for f in ("halo_emul.cpp", "resident_emul.cpp", "oracle.cpp", "decomp.cpp")]
     cmd = ["g++", "-std=c++17", "-O1", "-g", "-fsanitize=thread", "-pthread", "-I", str(ROOT / "include"),
            "-I", str(ROOT / "csrc/core"), str(main), *srcs, "-o", str(exe)]
     b = subprocess.run(cmd, capture_output=True, text=True)

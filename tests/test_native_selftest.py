@@ -13,7 +13,7 @@ from pathlib import Path
 import pytest
 
 ROOT = Path(__file__).resolve().parent.parent
-SOURCES = ["decomp.cpp", "cli.cpp", "rawio.cpp", "oracle.cpp", "halo_emul.cpp"]
+SOURCES = ["decomp.cpp", "cli.cpp", "rawio.cpp", "oracle.cpp", "halo_emul.cpp", "resident_emul.cpp"]
 
 
 @pytest.mark.skipif(shutil.which("g++") is None, reason="needs g++")
