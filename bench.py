@@ -302,16 +302,31 @@ def run_reference(a):
             f.write(rng.integers(0, 256, size=(min(rows, H - r), W * ch), dtype=np.uint8).tobytes())
     times, fail = [], None
     env = dict(os.environ, CUDA_VISIBLE_DEVICES=os.environ.get("CUDA_VISIBLE_DEVICES", "0").split(",")[0])
+    # Every step is a fresh process of the reference (context creation, PTX JIT from the compute
+    # cache, file I/O), ~50 s each on the default config.  If warm-up + steps would run past the
+    # budget (B200CONV_REF_MAX_SECONDS, default 900), warm-ups are trimmed first (never below 1),
+    # then steps (never below 1); the JSON reports the counts actually run.
+    budget = float(os.environ.get("B200CONV_REF_MAX_SECONDS", "900"))
+    warmup, steps, trimmed = a.warmup, a.steps, False
     wall0 = time.perf_counter()
-    for i in range(a.warmup + a.steps):
+    i = 0
+    while i < warmup + steps:
+        t_run = time.perf_counter()
         p = subprocess.run([str(exe), "bench.raw", str(W), str(H), str(a.reps), a.color], cwd=tmp, env=env,
                            capture_output=True, text=True)
+        t_run = time.perf_counter() - t_run
         m = re.search(r"Execution time: ([0-9.]+) sec", p.stdout)
         if p.returncode != 0 or not m:
             fail = (p.stderr.strip() or p.stdout.strip() or f"exit {p.returncode}")[:300]
             break
-        if i >= a.warmup:
+        if i >= warmup:
             times.append(float(m.group(1)))
+        i += 1
+        if i == 1:   # one run measured: does the plan fit the budget?
+            while warmup > 1 and t_run * (warmup + steps) > budget:
+                warmup, trimmed = warmup - 1, True
+            while steps > 1 and t_run * (warmup + steps) > budget:
+                steps, trimmed = steps - 1, True
     wall = time.perf_counter() - wall0
     for f in tmp.iterdir():
         f.unlink()
@@ -324,10 +339,10 @@ def run_reference(a):
     value = W * H * a.reps / sec / 1e9
     print(json.dumps({
         "metric": "gigapixel-iterations/sec", "value": value, "unit": "Gpix-it/s", "n_gpus": a.gpus,
-        "steps": a.steps, "warmup": a.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True,
+        "steps": steps, "warmup": warmup, "ms_per_step": sec * 1e3, "higher_is_better": True,
         "scaling": "weak" if a.weak else "strong", "vs_baseline": value / PUBLISHED[a.color],
         "dtype": "uint8 in/out, fp32+fp64 arithmetic", "data": "synthetic random uint8 .raw file",
-        "impl": "reference",
+        "impl": "reference", "requested": {"steps": a.steps, "warmup": a.warmup, "trimmed_to_time_budget": trimmed},
         "config": {"model": f"3x3 gaussian blur {W}x{H} {a.color}", "width": W, "height": H, "color": a.color,
                    "repetitions": a.reps, "effective_iterations": iters,
                    "parallelism": "single GPU (the reference CUDA program cannot use more)",
