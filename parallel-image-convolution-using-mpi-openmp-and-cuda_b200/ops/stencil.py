@@ -63,6 +63,13 @@ class Engine:
         except Exception:
             pass
 
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+        return False
+
     # -- geometry -----------------------------------------------------------
     @property
     def block_shape(self):
@@ -220,6 +227,13 @@ class BlurPipeline:
         self.wait()
         for e in self.engines:
             e.close()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+        return False
 
 
 def stencil_step(src: torch.Tensor, dst: torch.Tensor, rows: int, row_bytes: int, channels: int,

@@ -61,6 +61,13 @@ class ShardedBlur:
             dist.barrier(group=self.group)
         self.engine.close()
 
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()   # collective: every rank leaves the block together
+        return False
+
     def load(self, block: torch.Tensor):
         """Copy this rank's block in and run the initial halo exchange (collective)."""
         self.engine.load(block)
