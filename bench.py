@@ -226,6 +226,40 @@ def run_b200conv(a):
                "api": "ShardedBlur.load(pinned) / run / iterations_done / store(pinned), one image at a time",
                "h2d_bytes_per_step": nbytes * world, "d2h_bytes_per_step": nbytes * world}
 
+    # ---- scaling diagnostics (several GPUs): every rank's own device time of the coupled loop, and
+    #      the same block alone on that GPU (no neighbours, same strip width and rows per warp).  A
+    #      coupled loop runs at the pace of its slowest GPU, so these two lists separate protocol
+    #      cost from GPU-to-GPU variation.  Never allowed to break the result line.
+    per_rank_ms = solo_ms_per_rank = None
+    if world > 1:
+        def gather_floats(x):
+            t = torch.tensor([x], dtype=torch.float64, device=f"cuda:{local}")
+            parts = [torch.empty_like(t) for _ in range(world)]
+            dist.all_gather(parts, t)
+            return [float(p.item()) for p in parts]
+
+        per_rank_ms = gather_floats(ev0.elapsed_time(ev1) / a.steps)
+        solo_ms = float("nan")
+        try:
+            m = re.search(r"strip=(\d+)B .*chunks=\d+\(x(\d+) rows\)", desc)
+            if m and not a.check_every:
+                solo = b200conv.Engine(shape[1], shape[0], ch, device=local, boundary="zero", tb=a.tb, kernel=a.kernel,
+                                       strip_bytes=int(m.group(1)), chunk_rows=int(m.group(2)))
+                solo.load(host_in)
+                solo.run(a.reps)
+                torch.cuda.synchronize()
+                s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                s0.record()
+                for _ in range(a.steps):
+                    solo.run(a.reps)
+                s1.record()
+                torch.cuda.synchronize()
+                solo_ms = s0.elapsed_time(s1) / a.steps
+                solo.close()
+        except Exception:  # noqa: BLE001
+            solo_ms = float("nan")
+        solo_ms_per_rank = gather_floats(solo_ms)
+
     if rank == 0:
         roof = 6555.5e9 / 2 / ch / 1e9 * world  # k=1 HBM roofline, MEASURED_PEAKS.json copy bandwidth
         try:
@@ -253,6 +287,11 @@ def run_b200conv(a):
             "clocks": sampler.summary() if sampler else None,
             "e2e": e2e,
         }
+        if per_rank_ms is not None:
+            clean = lambda v: [None if x != x else round(x, 4) for x in v]  # noqa: E731  (NaN -> null)
+            out["per_rank"] = {"coupled_ms_per_step": clean(per_rank_ms),
+                               "block_alone_ms_per_step": clean(solo_ms_per_rank),
+                               "note": "block_alone = this rank's block on its GPU without neighbours, same plan"}
         print(json.dumps(out), flush=True)
     if eng is not None:
         eng.close()
