@@ -117,6 +117,34 @@ void blur_cuda_compat_rgb(const uint8_t *in, uint8_t *out, int W, int H, int rep
     memcpy(out, a.data(), (size_t)((int64_t)W * H * 3));
 }
 
+// Gaussian rows [r0, r1) of a framed buffer, separable and in 16-bit lanes so that the compiler can
+// vectorise it: h(x) = p(x-ch) + 2 p(x) + p(x+ch) per row (at most 1020), out = (h_up + 2 h + h_dn) >> 4.
+// Three h rows rotate through a small scratch buffer.  Same bytes as tap9 (exact integers).
+#if defined(__GNUC__) && defined(__x86_64__) && !defined(__SANITIZE_THREAD__) && !defined(__SANITIZE_ADDRESS__)
+__attribute__((target_clones("avx2", "default")))
+#endif
+void gauss_rows(const uint8_t *__restrict src, uint8_t *__restrict dst, int64_t pitch, int r0, int r1, int row_bytes,
+                int ch) {
+    std::vector<uint16_t> scratch((size_t)row_bytes * 3);
+    uint16_t *h[3] = {scratch.data(), scratch.data() + row_bytes, scratch.data() + 2 * (size_t)row_bytes};
+    auto hrow = [&](int r, uint16_t *__restrict o) {
+        const uint8_t *__restrict s = src + (int64_t)r * pitch;
+        for (int x = 0; x < row_bytes; ++x) o[x] = (uint16_t)(s[x - ch] + 2 * s[x] + s[x + ch]);
+    };
+    hrow(r0 - 1, h[0]);
+    hrow(r0, h[1]);
+    for (int r = r0; r < r1; ++r) {
+        hrow(r + 1, h[2]);
+        const uint16_t *__restrict a = h[0], *__restrict b = h[1], *__restrict c = h[2];
+        uint8_t *__restrict d = dst + (int64_t)r * pitch;
+        for (int x = 0; x < row_bytes; ++x) d[x] = (uint8_t)((a[x] + 2 * b[x] + c[x]) >> 4);
+        uint16_t *t = h[0];
+        h[0] = h[1];
+        h[1] = h[2];
+        h[2] = t;
+    }
+}
+
 }  // namespace
 
 namespace b2c {
@@ -182,6 +210,10 @@ int b2c_stencil_step_host(const uint8_t *src, uint8_t *dst, int64_t pitch, int r
     }
     const Weights w = make_weights(filter);
     auto band = [&](int r0, int r1) {
+        if (filter == B2C_GAUSSIAN) {
+            gauss_rows(src, dst, pitch, r0, r1, row_bytes, ch);
+            return;
+        }
         for (int r = r0; r < r1; ++r) {
             const uint8_t *s = src + (int64_t)r * pitch;
             uint8_t *d = dst + (int64_t)r * pitch;
