@@ -233,6 +233,40 @@ int b2c_stencil_step_host(const uint8_t *src, uint8_t *dst, int64_t pitch, int r
     return B2C_OK;
 }
 
+int b2c_blur_host(const uint8_t *in, uint8_t *out, int W, int H, int ch, int reps, int boundary, int filter,
+                  int threads) {
+    if (boundary == B2C_CUDA_COMPAT) return b2c_oracle_blur(in, out, W, H, ch, reps, boundary, filter);
+    if (!in || !out || W <= 0 || H <= 0 || (ch != 1 && ch != 3) || reps < 0 ||
+        (boundary != B2C_ZERO && boundary != B2C_TORUS) || filter < B2C_GAUSSIAN || filter > B2C_EDGE) {
+        b2c::set_error("blur_host: bad arguments");
+        return B2C_EINVAL;
+    }
+    const int64_t bw = (int64_t)W * ch, pitch = b2c::round_up(bw + 2 * ch, 64);
+    if (bw > (1ll << 30)) {
+        b2c::set_error("blur_host: row too wide");
+        return B2C_ETOOBIG;
+    }
+    std::vector<uint8_t> a((size_t)(pitch * (H + 2)), 0), b(a.size(), 0);
+    for (int r = 0; r < H; ++r) memcpy(&a[(size_t)((r + 1) * pitch + ch)], in + r * bw, (size_t)bw);
+    uint8_t *src = a.data(), *dst = b.data();
+    for (int t = 0; t < reps; ++t) {
+        if (boundary == B2C_TORUS) {
+            for (int r = 1; r <= H; ++r) {  // wrap columns, then rows (corners included)
+                uint8_t *row = src + r * pitch;
+                memcpy(row, row + bw, (size_t)ch);
+                memcpy(row + ch + bw, row + ch, (size_t)ch);
+            }
+            memcpy(src, src + (int64_t)H * pitch, (size_t)(bw + 2 * ch));
+            memcpy(src + (int64_t)(H + 1) * pitch, src + pitch, (size_t)(bw + 2 * ch));
+        }
+        const int rc = b2c_stencil_step_host(src + pitch + ch, dst + pitch + ch, pitch, H, (int)bw, ch, filter, threads);
+        if (rc != B2C_OK) return rc;
+        std::swap(src, dst);
+    }
+    for (int r = 0; r < H; ++r) memcpy(out + r * bw, src + (int64_t)(r + 1) * pitch + ch, (size_t)bw);
+    return B2C_OK;
+}
+
 int b2c_oracle_blur_sharded(const uint8_t *in, uint8_t *out, int W, int H, int ch, int reps,
                             int boundary, int P, int Q, int tb) {
     if (!in || !out || W <= 0 || H <= 0 || (ch != 1 && ch != 3) || reps < 0 || P <= 0 || Q <= 0 ||

@@ -1,6 +1,6 @@
 // b200conv — native launcher with the reference's command line.
 //
-//   b200conv image.raw width height repetitions grey|rgb [--gpus N] [--boundary ...] ...
+//   b200conv image.raw width height repetitions grey|rgb [--gpus N] [--boundary ...] ... [--cpu N|all]
 //
 // Replaces `mpiexec -n N ./mpi_convolution ...` (README.md:19-23) and `./cuda_convolution ...`
 // (README.md:32-34): the launcher forks one worker process per GPU (the MPI rank analogue,
@@ -240,6 +240,57 @@ void write_json(const b2c_cli &cli, int n, int P, int Q, const Shared *sh, doubl
     fclose(f);
 }
 
+// --cpu N|all: the whole program on host threads, no CUDA call at all (a machine without a GPU, or a
+// quick check).  Same files, same output lines; --gpus, --kernel, --tb, --check-every and
+// --checkpoint-every do not apply.  This is the role the reference's MPI / MPI+OpenMP programs play.
+int run_on_host(const b2c_cli &cli, double t_start) {
+    const long long row = (long long)cli.width * cli.channels, bytes = row * cli.height;
+    if (cli.width <= 0 || cli.height <= 0 || row > (1ll << 30)) {
+        fprintf(stderr, "bad image size\n");
+        return EXIT_FAILURE;
+    }
+    std::vector<uint8_t> img((size_t)bytes);
+    double t = now_ms();
+    if (b2c_read_block(cli.image, img.data(), row, cli.width, cli.height, cli.channels, 0, 0, cli.height, cli.width) < 0) {
+        fprintf(stderr, "%s\n", b2c_last_error());
+        return EXIT_FAILURE;
+    }
+    const double read_ms = now_ms() - t;
+    t = now_ms();
+    if (b2c_blur_host(img.data(), img.data(), cli.width, cli.height, cli.channels, cli.repetitions, cli.boundary,
+                      cli.filter, cli.cpu < 0 ? 0 : cli.cpu) != B2C_OK) {
+        fprintf(stderr, "%s\n", b2c_last_error());
+        return EXIT_FAILURE;
+    }
+    const double loop_ms = now_ms() - t;
+    char out_name[4096];
+    b2c_output_name(cli.image, out_name, sizeof out_name);
+    t = now_ms();
+    if (b2c_write_block(out_name, img.data(), row, cli.width, cli.height, cli.channels, 0, 0, cli.height, cli.width, 1) < 0) {
+        fprintf(stderr, "%s\n", b2c_last_error());
+        return EXIT_FAILURE;
+    }
+    const double write_ms = now_ms() - t;
+    const double total_s = (now_ms() - t_start) * 1e-3;
+    printf("%f\n", loop_ms * 1e-3);                       // mpi_convolution.c:274
+    printf("Execution time: %.3f sec\n", total_s);        // cuda/main.c:49
+    if (cli.profile)
+        fprintf(stderr, "host: read=%.3fms loop=%.3fms write=%.3fms threads=%d\n", read_ms, loop_ms, write_ms, cli.cpu);
+    if (cli.json) {
+        FILE *f = fopen(cli.json, "w");
+        if (f) {
+            fprintf(f, "{\"image\": \"%s\", \"width\": %d, \"height\": %d, \"channels\": %d, \"repetitions\": %d, "
+                       "\"device\": \"host\", \"threads\": %d, \"loop_seconds\": %.6f, \"total_seconds\": %.6f, "
+                       "\"gpix_it_per_s\": %.3f}\n",
+                    json_escape(cli.image).c_str(), cli.width, cli.height, cli.channels, cli.repetitions, cli.cpu,
+                    loop_ms * 1e-3, total_s,
+                    loop_ms > 0 ? (double)cli.width * cli.height * cli.repetitions / (loop_ms * 1e-3) / 1e9 : 0.0);
+            fclose(f);
+        }
+    }
+    return EXIT_SUCCESS;
+}
+
 }  // namespace
 
 int main(int argc, char **argv) {
@@ -251,13 +302,20 @@ int main(int argc, char **argv) {
         fputs(buf, stderr);
         return EXIT_FAILURE;
     }
+    if (cli.cpu != 0) {
+        if (access(cli.image, R_OK) != 0) {
+            fprintf(stderr, "cannot open %s\n", cli.image);  // cuda/main.c:24
+            return EXIT_FAILURE;
+        }
+        return run_on_host(cli, t_start);
+    }
     int n = cli.gpus;
     int P = 0, Q = 0;
     if (n <= 0) {
         // default = every visible GPU that the image divides over (the `mpiexec -n` analogue)
         n = count_gpus_in_child();
         if (n <= 0) {
-            fprintf(stderr, "%s: no CUDA device\n", argv[0]);
+            fprintf(stderr, "%s: no CUDA device (add --cpu N to run on host threads)\n", argv[0]);
             return EXIT_FAILURE;
         }
         if (n > kMaxWorkers) n = kMaxWorkers;

@@ -96,6 +96,7 @@ typedef struct b2c_cli {
     int checkpoint_every; /* write the image every N iterations, 0 = off */
     int profile;        /* per-phase timings on stderr */
     const char *json;   /* path for the JSON report, NULL = none */
+    int cpu;            /* --cpu N|all: run on N host threads (-1 = all cores) instead of GPUs; 0 = GPUs */
 } b2c_cli;
 
 /* Grammar of Usage() mpi/mpi_convolution.c:328-348 and Initialization()
@@ -134,6 +135,12 @@ int b2c_oracle_blur(const uint8_t *in, uint8_t *out, int width, int height, int 
  * Result must equal b2c_oracle_blur on every grid (decomposition independence). */
 int b2c_oracle_blur_sharded(const uint8_t *in, uint8_t *out, int width, int height, int channels,
                             int repetitions, int boundary, int grid_rows, int grid_cols, int tb);
+
+/* Whole blur on host threads (tight H x W*CH images, `in` and `out` may alias): the no-GPU fallback of
+ * the launcher (`--cpu N`) and of the Python package.  ZERO / TORUS run b2c_stencil_step_host on
+ * framed ping-pong buffers (threads = 0: all cores), CUDA_COMPAT runs the oracle.  Exact. */
+int b2c_blur_host(const uint8_t *in, uint8_t *out, int width, int height, int channels, int repetitions,
+                  int boundary, int filter, int threads);
 
 /* Threaded host model of the multi-GPU protocol: one thread per rank, framed
  * ping-pong buffers, per-direction epoch flags (release/acquire), ring pushes

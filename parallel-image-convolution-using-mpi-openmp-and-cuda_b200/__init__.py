@@ -15,7 +15,7 @@ MPI+OpenMP and CUDA programs) on one C++/CUDA core:
 """
 from . import _lib
 from ._lib import B2CError
-from .ops import (BlurPipeline, Engine, blur, blur_file, clear_engine_cache, numpy_oracle, reference_oracle, sharded_oracle,
+from .ops import (BlurPipeline, Engine, blur, blur_cpu, blur_file, clear_engine_cache, numpy_oracle, reference_oracle, sharded_oracle,
                   stencil_step)
 from .parallel import LocalGrid, ShardedBlur, ShardedPipeline, block_of, decompose, neighbours, rows_division
 from . import models, ops, parallel, utils

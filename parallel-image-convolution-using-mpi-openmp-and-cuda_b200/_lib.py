@@ -42,7 +42,7 @@ class Cli(C.Structure):
     _fields_ = [("image", C.c_char_p), ("width", C.c_int), ("height", C.c_int), ("repetitions", C.c_int),
                 ("channels", C.c_int), ("gpus", C.c_int), ("boundary", C.c_int), ("filter", C.c_int),
                 ("tb", C.c_int), ("kernel", C.c_int), ("check_every", C.c_int), ("checkpoint_every", C.c_int),
-                ("profile", C.c_int), ("json", C.c_char_p)]
+                ("profile", C.c_int), ("json", C.c_char_p), ("cpu", C.c_int)]
 
 
 class B2CError(RuntimeError):
@@ -77,6 +77,7 @@ def _load() -> C.CDLL:
         "b2c_oracle_blur_sharded": (I, [u8p, u8p, I, I, I, I, I, I, I, I]),
         "b2c_emulate_halo_threads": (I, [u8p, u8p, I, I, I, I, I, I, I, C.POINTER(EmulOpts), C.POINTER(I)]),
         "b2c_stencil_step_host": (I, [u8p, u8p, L, I, I, I, I, I]),
+        "b2c_blur_host": (I, [u8p, u8p, I, I, I, I, I, I, I]),
         "b2c_default_opts": (None, [C.POINTER(Opts)]),
         "b2c_engine_create": (P, [I, I, I, I, I, I, I, C.POINTER(Opts)]),
         "b2c_engine_destroy": (None, [P]),

@@ -5,6 +5,7 @@
 ``numpy_oracle``      — an independent numpy restatement of ``out = (sum w*p) >> 4`` used to
                         cross-check the C++ oracle (mpi/mpi_convolution.c:301-322 semantics at
                         one rank; torus per README.md:63-66).
+``blur_cpu``          — the threaded, vectorised host path (what the launcher's ``--cpu N`` runs).
 ``sharded_oracle``    — host emulation of the multi-rank frame/epoch halo protocol.
 ``threaded_resident_model`` — one thread per CTA of the resident kernel (tile plan, ring/halo exchange images, epochs).
 ``threaded_halo_model`` — the same protocol with one thread per rank, atomics for the epoch flags
@@ -46,6 +47,16 @@ def reference_oracle(img, reps: int, boundary: str = "zero", filter: str = "gaus
     out = np.empty_like(flat)
     check(lib.b2c_oracle_blur(flat.ctypes.data, out.ctypes.data, w, h, ch, int(reps), BOUNDARY[boundary],
                               FILTER[filter]), "oracle_blur")
+    return restore(out)
+
+
+def blur_cpu(img, reps: int, boundary: str = "zero", filter: str = "gaussian", threads: int = 0):
+    """Whole blur on host threads (``b2c_blur_host``): the no-GPU path, exact, ndarray or CPU tensor in,
+    same kind out.  ``threads`` = 0 uses every core."""
+    flat, w, h, ch, restore = _as_image(img)
+    out = np.empty_like(flat)
+    check(lib.b2c_blur_host(flat.ctypes.data, out.ctypes.data, w, h, ch, int(reps), BOUNDARY[boundary],
+                            FILTER[filter], int(threads)), "blur_host")
     return restore(out)
 
 

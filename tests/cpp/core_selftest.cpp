@@ -78,6 +78,10 @@ static void test_cli() {
         EXPECT(b2c_parse_cli(1, (char **)argv, &c) == B2C_EINVAL);
     }
     {
+        const char *argv3[] = {"prog", "img.raw", "8", "8", "2", "rgb", "--cpu", "all"};
+        EXPECT(b2c_parse_cli(8, (char **)argv3, &c) == B2C_OK && c.cpu == -1);
+        const char *argv4[] = {"prog", "img.raw", "8", "8", "2", "rgb", "--cpu", "0"};
+        EXPECT(b2c_parse_cli(8, (char **)argv4, &c) == B2C_EINVAL);
         const char *argv[] = {"prog", "img.raw", "8", "8", "2", "rgb", "--boundary"};  // value missing
         EXPECT(b2c_parse_cli(7, (char **)argv, &c) == B2C_EINVAL);
         const char *argv2[] = {"prog", "img.raw", "8", "8", "2", "rgb", "--no-such-flag", "1"};
@@ -184,7 +188,17 @@ static void test_host_step() {
                     EXPECT(!memcmp(&dst[(size_t)((r + 1) * pitch + ch)], &want[(size_t)(r * bw)], (size_t)bw));
                 EXPECT(dst[0] == 0x5A && dst[(size_t)(pitch + ch - 1)] == 0x5A);   // frame untouched
             }
+    for (int ch : {1, 3})   // whole blur on host threads, in place, against the oracle
+        for (int boundary : {B2C_ZERO, B2C_TORUS, B2C_CUDA_COMPAT})
+            for (int W : {1, 2, 31})
+                for (int H : {1, 3, 17}) {
+                    std::vector<uint8_t> img = noise((size_t)W * H * ch, (unsigned)(W + 7 * H)), want(img.size());
+                    EXPECT(b2c_oracle_blur(img.data(), want.data(), W, H, ch, 4, boundary, B2C_GAUSSIAN) == B2C_OK);
+                    EXPECT(b2c_blur_host(img.data(), img.data(), W, H, ch, 4, boundary, B2C_GAUSSIAN, 2) == B2C_OK);
+                    EXPECT(img == want);
+                }
     std::vector<uint8_t> a(64, 0);
+    EXPECT(b2c_blur_host(a.data(), a.data(), 4, 4, 2, 1, B2C_ZERO, B2C_GAUSSIAN, 1) == B2C_EINVAL);
     EXPECT(b2c_stencil_step_host(a.data(), a.data(), 8, 2, 4, 1, B2C_GAUSSIAN, 1) == B2C_EINVAL);   // in place
     EXPECT(b2c_stencil_step_host(a.data(), a.data() + 32, 4, 2, 4, 1, B2C_GAUSSIAN, 1) == B2C_EINVAL);   // pitch too small
 }

@@ -37,6 +37,26 @@ def test_cannot_divide_and_missing_file(launcher, tmp_path):
     assert p.returncode == 1 and "cannot open nope.raw" in p.stderr
 
 
+@pytest.mark.parametrize("color,boundary,cpu", [("grey", "zero", "1"), ("rgb", "zero", "3"), ("rgb", "torus", "all"),
+                                                ("grey", "cuda-compat", "2")])
+def test_whole_program_on_host_threads(launcher, tmp_path, color, boundary, cpu):
+    # --cpu N|all: no CUDA call at all; same files, same two output lines as the GPU path
+    ch = 1 if color == "grey" else 3
+    img = np.random.default_rng(5).integers(0, 256, (37, 52) if ch == 1 else (37, 52, ch), dtype=np.uint8)
+    write_raw(tmp_path / "in.raw", img)
+    rep = tmp_path / "report.json"
+    p = run(["in.raw", 52, 37, 6, color, "--cpu", cpu, "--boundary", boundary, "--json", rep], tmp_path)
+    assert p.returncode == 0, p.stderr
+    lines = p.stdout.splitlines()
+    assert len(lines) == 2 and float(lines[0]) >= 0 and lines[1].startswith("Execution time: ")
+    out = read_raw(tmp_path / "blur_in.raw", 52, 37, ch)
+    assert (out == reference_oracle(img, 6, boundary)).all()
+    d = json.loads(rep.read_text())
+    assert d["device"] == "host" and d["repetitions"] == 6
+    assert run(["in.raw", 52, 37, 6, color, "--cpu", "0"], tmp_path).returncode == 1      # 0 threads is not a count
+    assert run(["nope.raw", 52, 37, 6, color, "--cpu", "1"], tmp_path).returncode == 1
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("color,boundary", [("grey", "zero"), ("rgb", "zero"), ("rgb", "torus"), ("grey", "cuda-compat")])
 def test_single_gpu_program(launcher, tmp_path, color, boundary):

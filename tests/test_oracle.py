@@ -93,3 +93,19 @@ def test_float_filters_follow_reference_op_order(name):
                 acc = (acc + (p[i:i + x.shape[0], j:j + x.shape[1]] * w[i, j]).astype(np.float32)).astype(np.float32)
         x = acc.astype(np.uint8)
     assert (got == x).all()
+
+
+@pytest.mark.parametrize("boundary", ["zero", "torus", "cuda-compat"])
+@pytest.mark.parametrize("threads", [1, 3, 0])
+def test_threaded_host_blur_equals_oracle(boundary, threads):
+    from b200conv import blur_cpu
+    rng = np.random.default_rng(12)
+    for shape in ((1, 1), (2, 5), (33, 47), (20, 31, 3), (3, 3, 3)):
+        img = rng.integers(0, 256, shape, dtype=np.uint8)
+        for reps in (0, 1, 5):
+            assert (blur_cpu(img, reps, boundary, threads=threads) == reference_oracle(img, reps, boundary)).all()
+    if boundary != "cuda-compat":
+        img = rng.integers(0, 256, (19, 23), dtype=np.uint8)
+        for filt in ("box", "edge"):
+            assert (blur_cpu(img, 3, boundary, filter=filt, threads=threads) ==
+                    reference_oracle(img, 3, boundary, filter=filt)).all()
