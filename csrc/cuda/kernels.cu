@@ -302,3 +302,12 @@ cudaError_t launch_set_u32(unsigned int *p, unsigned int v, cudaStream_t s) {
 }
 
 }  // namespace b2c
+
+// The work-item order of the streaming kernels, callable on the host so that a CPU test can check
+// that it visits every (band, chunk) exactly once for every plan (a gap or a duplicate would leave a
+// per-direction arrival counter short and hang the neighbours).
+extern "C" int b2c_debug_map_work(int id, int nbands, int nchunks, int nbw, int nbe, int *band, int *chunk) {
+    if (id < 0 || nbands <= 0 || nchunks <= 0 || id >= nbands * nchunks || !band || !chunk) return B2C_EINVAL;
+    b2c::map_work(id, nbands, nchunks, nbw, nbe, *band, *chunk);
+    return B2C_OK;
+}

@@ -353,7 +353,7 @@ __device__ __forceinline__ void stream_band(const PassParams &p, Feed &feed, con
 
 // Ring-first work order: top chunk, bottom chunk, then the west/east bands of
 // the middle chunks, then the interior.
-__device__ __forceinline__ void map_work(int id, int NB, int NC, int nbw, int nbe, int &band, int &chunk) {
+__host__ __device__ __forceinline__ void map_work(int id, int NB, int NC, int nbw, int nbe, int &band, int &chunk) {
     if (NC <= 2 || NB <= nbw + nbe) {  // everything is ring
         chunk = id / NB; band = id % NB; return;
     }

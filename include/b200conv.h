@@ -303,6 +303,10 @@ int b2c_blur_device_noalloc(const uint8_t *d_in, int64_t in_pitch, uint8_t *d_ou
 int b2c_stencil_step_device(const uint8_t *src, uint8_t *dst, int64_t pitch, int rows, int row_bytes,
                             int channels, int filter, void *stream);
 
+/* Test hook (host only): work item `id` -> (band, chunk) in the ring-first order the streaming kernels
+ * use.  Lets a CPU test prove that every plan visits each (band, chunk) exactly once. */
+int b2c_debug_map_work(int id, int nbands, int nchunks, int nbw, int nbe, int *band, int *chunk);
+
 /* Whole-program equivalent of cuda/main.c:10-53 (read file, blur, write
  * blur_<name>) on one GPU; returns loop milliseconds in *loop_ms. */
 int b2c_blur_file(const char *image, int width, int height, int channels, int repetitions,
