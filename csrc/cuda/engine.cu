@@ -947,6 +947,31 @@ int b2c_engine_describe(const b2c_engine *e, char *buf, size_t buflen) {
     return B2C_OK;
 }
 
+// Test hook (host only, no CUDA call that matters): the band/chunk plan the engine would use for one
+// rank's block, so that CPU property tests can check the invariants the kernels rely on.
+// out = {hlo, vw, nbands, nchunks, chunk_rows, nbw, nbe, K, SB, F}.
+int b2c_debug_band_plan(int rows, int cols, int channels, int has_neighbours, int tb, int strip_bytes, int chunk_rows,
+                        int kernel, int sm_count, int out[10]) {
+    if (rows <= 0 || cols <= 0 || (channels != 1 && channels != 3) || !out) return B2C_EINVAL;
+    if ((long long)cols * channels > (1ll << 30)) return B2C_ETOOBIG;
+    b2c_engine e;
+    b2c_default_opts(&e.opts);
+    e.opts.tb = tb;
+    e.opts.strip_bytes = strip_bytes;
+    e.opts.chunk_rows = chunk_rows;
+    e.opts.kernel = kernel;
+    e.R = rows, e.C = cols, e.CH = channels, e.bw = cols * channels;
+    e.W = cols, e.H = rows;
+    e.any_nb = has_neighbours != 0;
+    for (int &n : e.nb) n = has_neighbours ? 0 : -1;
+    e.sm_count = sm_count > 0 ? sm_count : 148;
+    choose_plan(&e);
+    const BandPlan bp = make_band_plan(&e, e.K);
+    const int v[10] = {bp.hlo, bp.vw, bp.nbands, bp.nchunks, bp.chunk_rows, bp.nbw, bp.nbe, e.K, e.SB, e.F};
+    memcpy(out, v, sizeof v);
+    return B2C_OK;
+}
+
 int b2c_engine_set_delay(b2c_engine *e, int64_t cycles) {
     if (!e) return B2C_EINVAL;
     e->delay = cycles;

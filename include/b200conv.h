@@ -307,6 +307,11 @@ int b2c_stencil_step_device(const uint8_t *src, uint8_t *dst, int64_t pitch, int
  * use.  Lets a CPU test prove that every plan visits each (band, chunk) exactly once. */
 int b2c_debug_map_work(int id, int nbands, int nchunks, int nbw, int nbe, int *band, int *chunk);
 
+/* Test hook (host only): the streaming kernels' plan for one rank's block of rows x cols pixels.
+ * out = {hlo, vw, nbands, nchunks, chunk_rows, nbw, nbe, K, strip_bytes, halo_depth}. */
+int b2c_debug_band_plan(int rows, int cols, int channels, int has_neighbours, int tb, int strip_bytes,
+                        int chunk_rows, int kernel, int sm_count, int out[10]);
+
 /* Whole-program equivalent of cuda/main.c:10-53 (read file, blur, write
  * blur_<name>) on one GPU; returns loop milliseconds in *loop_ms. */
 int b2c_blur_file(const char *image, int width, int height, int channels, int repetitions,

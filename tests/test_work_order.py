@@ -41,3 +41,35 @@ def test_bad_arguments_are_refused():
     band, chunk = C.c_int(), C.c_int()
     assert lib.b2c_debug_map_work(6, 2, 3, 1, 1, C.byref(band), C.byref(chunk)) < 0
     assert lib.b2c_debug_map_work(-1, 2, 3, 1, 1, C.byref(band), C.byref(chunk)) < 0
+
+
+# ---- the band / chunk plan itself (b2c_debug_band_plan runs choose_plan + make_band_plan on the host)
+from hypothesis import given, settings  # noqa: E402
+from hypothesis import strategies as st  # noqa: E402
+
+
+@settings(max_examples=400, deadline=None)
+@given(rows=st.integers(1, 5000), cols=st.integers(1, 6000), ch=st.sampled_from([1, 3]), nb=st.booleans(),
+       tb=st.sampled_from([0, 1, 2, 4, 8]), strip=st.sampled_from([0, 4, 8, 16]), chunk=st.sampled_from([0, 1, 7, 64, 100000]),
+       kernel=st.sampled_from([0, 2, 3]))
+def test_plan_invariants_the_kernels_rely_on(rows, cols, ch, nb, tb, strip, chunk, kernel):
+    out = (C.c_int * 10)()
+    assert lib.b2c_debug_band_plan(rows, cols, ch, int(nb), tb, strip, chunk, kernel, 148, out) == 0
+    hlo, vw, nbands, nchunks, chunk_rows, nbw, nbe, K, SB, F = list(out)
+    bw = cols * ch
+    align = 16 if kernel == 3 else SB
+    assert K in (1, 2, 4, 8) and SB in (4, 8, 16) and K * (SB // 4) <= 16        # register budget
+    if nb:
+        assert K <= min(rows, cols) or K == 1                                   # a K-deep halo comes from one neighbour
+        assert F == K
+    # window of a band: [band*vw - hlo, +32*SB); it must hold K*CH bytes of overlap on both sides
+    assert vw > 0 and hlo % align == 0 and vw % align == 0
+    assert K * ch <= hlo <= 32                                                  # left frame is 32 bytes
+    assert 32 * SB - hlo - vw >= K * ch
+    assert nbands == -(-bw // vw) and nchunks == -(-rows // chunk_rows) and 1 <= chunk_rows <= rows
+    if nb:
+        # the whole F-deep ring must sit in the chunks / bands that push it
+        assert chunk_rows >= min(F, rows)
+        assert nbw == nbands or nbw * vw >= F * ch
+        assert nbe == nbands or (nbands - nbe) * vw <= bw - F * ch
+        assert 1 <= nbw <= nbands and 1 <= nbe <= nbands
