@@ -5,12 +5,17 @@
 // stencil_stream.cuh, kernels.cu: converge_kernel), restated with std::atomic:
 //
 //   * two framed ping-pong buffers per rank; pass t reads buf[(t-1)&1] and writes buf[t&1];
-//   * after a pass a rank stores the depth-F ring of its new block straight into the frames of
-//     its (up to 8) neighbours' buf[t&1], then release-stores epoch t+1 into the flag word the
-//     neighbour keeps for that direction;
-//   * before a pass a rank acquire-waits on the flag of every direction that has a neighbour —
-//     that covers both "my halos have arrived" and "the neighbour has finished reading the frame
-//     I am about to overwrite";
+//   * passes form groups of at most F iterations with ONE halo exchange per group: the first pass
+//     of a group acquire-waits on the data flag of every direction that has a neighbour; the
+//     passes in between also write the part of the frame that is still valid (the block extended
+//     by the iterations left in the group); the last pass stores the depth-F ring of its new block
+//     straight into the frames of its (up to 8) neighbours' buf[t&1], then release-stores epoch
+//     g+1 into the flag word the neighbour keeps for that direction;
+//   * a group of one pass needs nothing else (the neighbour's data flag also says that it has
+//     finished reading the frame about to be overwritten).  In a longer group the in-between
+//     passes read and write frames of both buffers, so the second-to-last pass publishes an "ack"
+//     epoch once it has read its frames, and the last pass waits for the neighbours' acks before
+//     it pushes;
 //   * ring results are published before the interior is written (the GPU orders ring warps first);
 //   * a check pass is followed by an all-to-all exchange of one "changed" bit through per-rank
 //     slots tagged with the check number and double-buffered by its parity; when nobody changed,
@@ -21,6 +26,7 @@
 // on the frames; with `single_slot_set` it reproduces the lost-tag hang that the parity fixes.
 // Nothing here is taken from the reference: mpi_convolution.c:158-234 has neither epochs, nor
 // diagonal neighbours, nor a convergence test.
+#include <algorithm>
 #include <atomic>
 #include <chrono>
 #include <memory>
@@ -38,28 +44,48 @@ struct Rank {
     std::vector<uint8_t> buf[2];
     int nb[8];
     std::atomic<uint32_t> flag[8];
+    std::atomic<uint32_t> ack[8];
     std::unique_ptr<std::atomic<uint32_t>[]> slots;  // 2 sets x n ranks
     int iters = 0;
 };
+
+enum { kWaitData = 1, kPostAck = 2, kWaitAck = 4, kPush = 8 };
 
 struct Pass {
     int k;
     bool check;
     int iters_after;
+    int ext;         // iterations left in the group after this pass
+    int mode;
+    bool group_end;
 };
 
-// Same rule as make_passes() in engine.cu: k in {K, K/2, .., 1}, a pass ends on every multiple of
-// check_every.
-std::vector<Pass> split_passes(int reps, int K, int ce) {
+// Same rule as make_passes() in engine.cu: groups of at most F iterations (a group also ends on
+// every multiple of check_every), each cut into passes of k in {K, K/2, .., 1}.
+std::vector<Pass> split_passes(int reps, int K, int F, int ce) {
     std::vector<Pass> v;
     int done = 0;
     while (done < reps) {
-        int limit = reps - done;
-        if (ce > 0) limit = std::min(limit, ce - done % ce);
-        int k = K;
-        while (k > limit) k >>= 1;
-        done += k;
-        v.push_back({k, ce > 0 && done % ce == 0, done});
+        int glen = std::min(reps - done, F);
+        if (ce > 0) glen = std::min(glen, ce - done % ce);
+        std::vector<int> ks;
+        for (int left = glen; left > 0;) {
+            int k = K;
+            while (k > left) k >>= 1;
+            ks.push_back(k);
+            left -= k;
+        }
+        const int n = (int)ks.size();
+        int ext = glen;
+        for (int j = 0; j < n; ++j) {
+            ext -= ks[j];
+            done += ks[j];
+            int mode = 0;
+            if (j == 0) mode |= kWaitData;
+            if (n >= 2 && j == n - 2) mode |= kPostAck;
+            if (j == n - 1) mode |= kPush | (n >= 2 ? kWaitAck : 0);
+            v.push_back({ks[j], j == n - 1 && ce > 0 && done % ce == 0, done, ext, mode, j == n - 1});
+        }
     }
     return v;
 }
@@ -112,6 +138,12 @@ struct World {
             if (me.nb[d] >= 0) ranks[me.nb[d]].flag[b2c::opposite_dir(d)].store(epoch, std::memory_order_release);
     }
 
+    void publish_ack(int q, uint32_t epoch) {
+        Rank &me = ranks[q];
+        for (int d = 0; d < 8; ++d)
+            if (me.nb[d] >= 0) ranks[me.nb[d]].ack[b2c::opposite_dir(d)].store(epoch, std::memory_order_release);
+    }
+
     void run_rank(int q, const uint8_t *in, uint8_t *out) {
         Rank &me = ranks[q];
         std::mt19937 rng(o.seed * 7919u + (unsigned)q);
@@ -153,33 +185,57 @@ struct World {
             unsigned changed = 0;
             if (!converged) {
                 jitter();
-                for (int d = 0; d < 8; ++d)
-                    if (me.nb[d] >= 0 &&
-                        !wait_for([&] { return (int32_t)(me.flag[d].load(std::memory_order_acquire) - epoch) >= 0; }))
-                        return;
-                t0 = me.buf[cur];
+                if (ps.mode & kWaitData)
+                    for (int d = 0; d < 8; ++d)
+                        if (me.nb[d] >= 0 &&
+                            !wait_for([&] { return (int32_t)(me.flag[d].load(std::memory_order_acquire) - epoch) >= 0; }))
+                            return;
+                if (ps.mode & kWaitAck)
+                    for (int d = 0; d < 8; ++d)
+                        if (me.nb[d] >= 0 &&
+                            !wait_for([&] { return (int32_t)(me.ack[d].load(std::memory_order_acquire) - epoch) >= 0; }))
+                            return;
+                // The block is extended into the frame by the iterations left in the group, on the
+                // sides that have a neighbour (whole 16-byte strips west/east, like the kernel).
+                const int xn = me.nb[B2C_N] >= 0 ? ps.ext : 0, xs = me.nb[B2C_S] >= 0 ? ps.ext : 0;
+                const int64_t xcol = std::min<int64_t>(fb, b2c::round_up((int64_t)ps.ext * ch, 16));
+                const int64_t xw = me.nb[B2C_W] >= 0 ? xcol : 0, xe = me.nb[B2C_E] >= 0 ? xcol : 0;
+                // read only what the kernel reads: the extended block plus k rows / k*ch bytes around it
+                {
+                    const int ra = std::max(0, F - xn - ps.k), rb = std::min(rows, F + R + xs + ps.k);
+                    const int64_t ca = std::max<int64_t>(0, fb - xw - (int64_t)ps.k * ch);
+                    const int64_t cb = std::min<int64_t>(pitch, fb + bw + xe + (int64_t)ps.k * ch);
+                    t0.assign((size_t)(pitch * rows), 0);
+                    for (int r = ra; r < rb; ++r)
+                        memcpy(&t0[r * pitch + ca], &me.buf[cur][r * pitch + ca], (size_t)(cb - ca));
+                }
                 b2c::framed_iterations(t0, t1, rows, pitch, ch, F, fb, r0, c0b, H, (int64_t)W * ch, torus, ps.k);
-                auto copy_rows = [&](int ra, int rb, int64_t xa, int64_t xb) {
+                auto copy_rows = [&](int ra, int rb, int64_t xa, int64_t xb) {   // block-relative, may be negative
                     for (int r = ra; r < rb; ++r) {
                         const int64_t off = (r + F) * pitch + fb;
                         memcpy(&me.buf[cur ^ 1][off + xa], &t0[off + xa], (size_t)(xb - xa));
                         if (ps.check) changed |= memcmp(&t0[off + xa], &t1[off + xa], (size_t)(xb - xa)) != 0;
                     }
                 };
-                // ring first (top / bottom F rows, left / right fb bytes), then publish, then interior
+                // ring first (top / bottom F rows, left / right fb bytes, plus the extension), then
+                // publish, then interior
                 const int Ft = std::min(F, R), Fb = std::max(Ft, R - F);
                 const int64_t fl = std::min(fb, bw), fr = std::max(fl, bw - fb);
-                copy_rows(0, Ft, 0, bw);
-                copy_rows(Fb, R, 0, bw);
-                copy_rows(Ft, Fb, 0, fl);
-                copy_rows(Ft, Fb, fr, bw);
+                copy_rows(-xn, Ft, -xw, bw + xe);
+                copy_rows(Fb, R + xs, -xw, bw + xe);
+                copy_rows(Ft, Fb, -xw, fl);
+                copy_rows(Ft, Fb, fr, bw + xe);
                 jitter();
-                push_ring(q, cur ^ 1);
-                publish(q, epoch + 1);
+                if (ps.mode & kPush) {
+                    push_ring(q, cur ^ 1);
+                    publish(q, epoch + 1);
+                } else if (ps.mode & kPostAck) {
+                    publish_ack(q, epoch);
+                }
                 jitter();
                 copy_rows(Ft, Fb, fl, fr);
                 cur ^= 1;
-                epoch++;
+                if (ps.group_end) epoch++;
             }
             if (ps.check) {
                 ++seq;
@@ -228,15 +284,18 @@ extern "C" int b2c_emulate_halo_threads(const uint8_t *in, uint8_t *out, int W, 
     w.o = *opts;
     int K = opts->tb >= 8 ? 8 : (opts->tb >= 4 ? 4 : (opts->tb >= 2 ? 2 : 1));
     while (K > 1 && K > std::min(w.R, w.C)) K >>= 1;  // a k-deep halo comes from the adjacent rank only
-    w.F = K;
+    int F = K;
+    if (opts->halo_depth > 0) F = std::max(K, std::min({opts->halo_depth, 32, w.R, w.C}) / K * K);
+    w.F = F;
     w.bw = (int64_t)w.C * ch, w.fb = (int64_t)w.F * ch, w.pitch = w.bw + 2 * w.fb;
     w.rows = w.R + 2 * w.F;
-    w.passes = split_passes(reps, K, opts->check_every);
+    w.passes = split_passes(reps, K, F, opts->check_every);
     w.ranks = std::vector<Rank>((size_t)w.n);
     for (int q = 0; q < w.n; ++q) {
         Rank &r = w.ranks[q];
         b2c_neighbours(q, P, Q, boundary, r.nb);
         for (auto &f : r.flag) f.store(0);
+        for (auto &f : r.ack) f.store(0);
         r.slots.reset(new std::atomic<uint32_t>[2 * (size_t)w.n]);
         for (int k = 0; k < 2 * w.n; ++k) r.slots[k].store(0);
     }

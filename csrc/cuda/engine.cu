@@ -43,14 +43,21 @@ struct NvtxRange {
 };
 
 // Flag pad layout, in 32-bit words.  Every flag/counter sits on its own 128 B line.
-constexpr int kPadFlags = 0;          // 8 x 32
-constexpr int kPadCounters = 256;     // 8 x 32
-constexpr int kPadSlots = 512;        // 2 parities x kMaxRanks words
+constexpr int kPadFlags = 0;          // 8 x 32: data epochs, index = direction the ring came from
+constexpr int kPadCounters = 256;     // 8 x 32: ring-warp arrival counters
+constexpr int kPadSlots = 512;        // 2 parities x kMaxRanks words (convergence bits)
 constexpr int kPadChanged = 640;
 constexpr int kPadConverged = 641;
 constexpr int kPadConvergedAt = 642;
-constexpr int kPadWords = 1024;
+constexpr int kPadEpoch = 672;        // the epoch at the start of the current run (device-side mirror of e->epoch)
+constexpr int kPadBarrier = 704;      // kMaxRanks words: start-barrier sequence numbers, index = rank
+constexpr int kPadBarrierSkew = 768;  // 2 words (u64): cycles this rank waited in the last start barrier
+constexpr int kPadAcks = 1024;        // 8 x 32: ack epochs, index = direction of the acknowledging neighbour
+constexpr int kPadProf = 1280;        // 40 x u64 wait/publish counters (B200CONV_HALO_PROF=1)
+constexpr int kProfWords64 = 40;
+constexpr int kPadWords = 2048;
 static_assert(kPadSlots + 2 * kMaxRanks <= kPadChanged, "convergence slots overlap the next pad field");
+static_assert(kPadProf + 2 * kProfWords64 <= kPadWords, "profile counters overlap the end of the pad");
 
 struct Blob {  // what b2c_engine_export ships; must fit B2C_HANDLE_BYTES
     cudaIpcMemHandle_t buf[2];
@@ -60,14 +67,21 @@ struct Blob {  // what b2c_engine_export ships; must fit B2C_HANDLE_BYTES
 };
 static_assert(sizeof(Blob) <= B2C_HANDLE_BYTES, "blob too large");
 
+// One kernel launch of the iteration loop.  Passes form groups of at most F iterations; halos are
+// exchanged once per group (see HaloParams in stencil_stream.cuh).
 struct Pass {
-    int k;
-    bool check;
-    unsigned iters_after;
+    int k;                 // fused iterations
+    bool check;            // convergence check after this pass (always the last pass of its group)
+    unsigned iters_after;  // iterations completed after it, counted from the start of the run
+    int ext;               // iterations left in the group after this pass = how far the block is extended
+    int mode;              // kHalo* bits
+    bool group_end;
 };
 
 struct BandPlan {
     int hlo, vw, nbands, nchunks, chunk_rows, nbw, nbe;
+    int xn, xs, xwb, xeb;   // extension of the block into the frame: rows north/south, bytes west/east
+    int rows, bw;           // extended block
 };
 
 }  // namespace
@@ -93,17 +107,22 @@ struct b2c_engine {
     std::vector<void *> ipc_opened;
     // state
     int cur = 0;
-    uint32_t epoch = 0;      // pushes completed so far (same on every rank)
+    uint32_t epoch = 0;      // exchanges completed so far (same on every rank)
+    uint32_t epoch_dev = 0;  // what pad[kPadEpoch] holds once everything enqueued so far has run
+    uint32_t barrier_seq = 0;
     unsigned check_seq = 0;
     int iters_done = 0;
     bool pending_converge_fixup = false;
     std::vector<Pass> last_passes;
     uint32_t run_epoch0 = 0;
     int run_cur0 = 0;
+    std::vector<Pass> staged;   // b2c_engine_plan_run / b2c_engine_run_pass
     // plan
     int kernel = B2C_KERNEL_STREAM, K = 4, SB = 16, F = 1;
+    bool chunk_rows_fixed = false;   // the caller gave chunk_rows: never tuned
     int sm_count = 148;
     long long delay = 0;
+    bool prof = false;
     long long launches = 0;
     std::map<std::pair<int, int>, cudaGraphExec_t> graphs;
     NaiveWeights nw{};
@@ -114,19 +133,23 @@ struct b2c_engine {
     long long res_xpitch = 0;
     uint32_t *res_flags = nullptr;   // sm_count x 32 words, then the error word
     uint32_t res_epoch = 0;
-    mutable BandPlan plan_cache[9];
-    mutable bool plan_ok[9] = {false, false, false, false, false, false, false, false, false};
+    mutable std::map<std::pair<int, int>, BandPlan> plan_cache;   // key (k, ext)
 };
 
 namespace {
 
-// Window geometry of a k-stage pass for the engine's strip width.
-void band_geometry(const b2c_engine *e, int k, int *hlo, int *vw, int *nbands) {
+void drop_graphs(b2c_engine *e) {
+    for (auto &g : e->graphs) cudaGraphExecDestroy(g.second);
+    e->graphs.clear();
+}
+
+// Window geometry of a k-stage pass for the engine's strip width over a block `bw` bytes wide.
+void band_geometry(const b2c_engine *e, int k, int bw, int *hlo, int *vw, int *nbands) {
     // window start and band pitch: strip-aligned for per-lane LDGs, 16 B for TMA box origins
     const int align = e->kernel == B2C_KERNEL_TMA ? 16 : e->SB;
     *hlo = (int)round_up((long long)k * e->CH, align);
     *vw = (int)round_down(32 * e->SB - *hlo - k * e->CH, align);
-    *nbands = (int)ceil_div(e->bw, *vw);
+    *nbands = (int)ceil_div(bw, *vw);
 }
 
 // Modelled time of one k-stage pass (microseconds, relative) for `cr` rows per warp, from
@@ -138,7 +161,7 @@ void band_geometry(const b2c_engine *e, int k, int *hlo, int *vw, int *nbands) {
 //     there (the block scheduler back-fills), one exact wave is not (no back-fill).
 double plan_cost(const b2c_engine *e, int k, int cr) {
     int hlo, vw, nb;
-    band_geometry(e, k, &hlo, &vw, &nb);
+    band_geometry(e, k, e->bw, &hlo, &vw, &nb);
     int occ = e->kernel == B2C_KERNEL_TMA ? stream_tma_occupancy(k, e->SB, e->CH) : stream_occupancy(k, e->SB, e->CH);
     if (occ <= 0) occ = 4;
     const double wave = (double)e->sm_count * occ * kWarpsPerCta;
@@ -153,12 +176,17 @@ double plan_cost(const b2c_engine *e, int k, int cr) {
     return std::max(t_lat, t_thr);
 }
 
+// Shortest first / last chunk a plan may have.  With neighbours the F-deep ring must sit inside
+// the chunks that push it, and the chunks next to them must not reach into a frame (they do not
+// wait for flags): F covers the push, 2k covers the reads of the pass that acknowledges.
+int min_edge_chunk(const b2c_engine *e, int k) { return e->any_nb ? std::max(e->F, 2 * k) : 1; }
+
 double best_chunk_rows(const b2c_engine *e, int k, int *out) {
     static const int cand[] = {8, 12, 16, 24, 32, 48, 64, 96, 128, 192, 256, 384, 512};
     double best = 1e300;
     int best_cr = std::max(1, e->R);
     for (int c : cand) {
-        int cr = std::max(c, std::max(2 * k, e->F));
+        int cr = std::max(c, std::max(2 * k, min_edge_chunk(e, k)));
         cr = std::min(cr, std::max(e->R, 1));
         const double t = plan_cost(e, k, cr);
         if (t < best * 0.999) { best = t; best_cr = cr; }
@@ -168,64 +196,99 @@ double best_chunk_rows(const b2c_engine *e, int k, int *out) {
     return best;
 }
 
-BandPlan make_band_plan(const b2c_engine *e, int k) {
-    if (k >= 1 && k <= 8 && e->plan_ok[k]) return e->plan_cache[k];
+// Plan of a k-stage pass whose block is extended by `ext` iterations into the frame on every side
+// that has a neighbour (ext = 0: the block itself).
+BandPlan make_band_plan(const b2c_engine *e, int k, int ext) {
+    const auto key = std::make_pair(k, ext);
+    auto it = e->plan_cache.find(key);
+    if (it != e->plan_cache.end()) return it->second;
     BandPlan bp{};
     const int CH = e->CH;
-    band_geometry(e, k, &bp.hlo, &bp.vw, &bp.nbands);
+    bp.xn = e->nb[B2C_N] >= 0 ? ext : 0;
+    bp.xs = e->nb[B2C_S] >= 0 ? ext : 0;
+    // whole 16-byte strips; the bytes past ext*CH are computed from stale frame bytes and are never
+    // inside the dependency cone of a byte that is used later
+    bp.xwb = e->nb[B2C_W] >= 0 ? (int)round_up((long long)ext * CH, 16) : 0;
+    bp.xeb = e->nb[B2C_E] >= 0 ? (int)round_up((long long)ext * CH, 16) : 0;
+    bp.rows = e->R + bp.xn + bp.xs;
+    bp.bw = e->bw + bp.xwb + bp.xeb;
+    band_geometry(e, k, bp.bw, &bp.hlo, &bp.vw, &bp.nbands);
     int chunk_rows = e->opts.chunk_rows;
     if (chunk_rows <= 0) {
         best_chunk_rows(e, k, &chunk_rows);
         const int nc = (int)ceil_div(e->R, chunk_rows);
         chunk_rows = (int)ceil_div(e->R, nc);   // even out the last chunk
     }
-    chunk_rows = std::max(chunk_rows, e->F);
-    chunk_rows = std::min(chunk_rows, std::max(e->R, 1));
+    const int min_edge = min_edge_chunk(e, k);
+    chunk_rows = std::max(chunk_rows, min_edge);
+    chunk_rows = std::min(chunk_rows, std::max(bp.rows, 1));
     chunk_rows = std::max(chunk_rows, 1);
     bp.chunk_rows = chunk_rows;
-    bp.nchunks = (int)ceil_div(e->R, chunk_rows);
-    const int fb = e->F * CH;
-    bp.nbw = std::min(bp.nbands, (int)ceil_div(fb, bp.vw));
-    bp.nbe = bp.nbands - (int)(std::max(0, e->bw - fb) / bp.vw);
-    bp.nbe = std::max(1, std::min(bp.nbands, bp.nbe));
-    if (k >= 1 && k <= 8) {
-        e->plan_cache[k] = bp;
-        e->plan_ok[k] = true;
-    }
+    bp.nchunks = (int)ceil_div(bp.rows, chunk_rows);
+    // the last chunk takes whatever is left (stream_band); a remainder shorter than min_edge is
+    // merged into the chunk before it
+    if (bp.nchunks > 1 && bp.rows - (bp.nchunks - 1) * chunk_rows < min_edge) bp.nchunks--;
+    // Bands that belong to the west / east ring: those whose stored strips hold part of the F-deep
+    // ring (they push), and those whose window reaches into the frame (they wait / acknowledge).
+    const int fb = e->F * CH, win = 32 * e->SB;
+    const int nbw_push = (int)ceil_div(fb, bp.vw);
+    const int nbw_read = (int)ceil_div(bp.xwb + bp.hlo, bp.vw);
+    bp.nbw = std::max(1, std::min(bp.nbands, std::max(nbw_push, nbw_read)));
+    const int nbe_push = bp.nbands - (int)(std::max(0, bp.bw - fb) / bp.vw);
+    const long long reach = (long long)bp.bw - bp.xeb + bp.hlo - win;   // band b reads the frame iff b*vw > reach
+    const int first_reader = reach < 0 ? 0 : (int)(reach / bp.vw) + 1;
+    const int nbe_read = bp.nbands - std::min(bp.nbands, first_reader);
+    bp.nbe = std::max(1, std::min(bp.nbands, std::max(nbe_push, nbe_read)));
+    e->plan_cache[key] = bp;
     return bp;
 }
 
-void fill_pass_params(const b2c_engine *e, int k, bool check, int src_i, PassParams &p) {
-    const BandPlan bp = make_band_plan(e, k);
+void fill_pass_params(const b2c_engine *e, const Pass &ps, int src_i, bool device_epoch, PassParams &p) {
+    const BandPlan bp = make_band_plan(e, ps.k, ps.ext);
     memset(&p, 0, sizeof p);
-    p.src = e->base[src_i];
-    p.dst = e->base[src_i ^ 1];
+    const long long shift = (long long)bp.xn * e->pitch + bp.xwb;
+    p.src = e->base[src_i] - shift;
+    p.dst = e->base[src_i ^ 1] - shift;
     p.pitch = e->pitch;
-    p.rows = e->R;
-    p.bw = e->bw;
+    p.rows = bp.rows;
+    p.bw = bp.bw;
     p.nbands = bp.nbands;
     p.nchunks = bp.nchunks;
     p.chunk_rows = bp.chunk_rows;
     p.vw = bp.vw;
     p.hlo = bp.hlo;
+    p.org_x = kLeftPad - bp.xwb;
+    p.org_y = kFrameRows - bp.xn;
     const bool zero = e->opts.boundary == B2C_ZERO;
     p.zero_n = zero && e->nb[B2C_N] < 0;
     p.zero_s = zero && e->nb[B2C_S] < 0;
     p.zero_w = zero && e->nb[B2C_W] < 0;
     p.zero_e = zero && e->nb[B2C_E] < 0;
-    p.changed = check ? e->pad + kPadChanged : nullptr;
+    p.changed = ps.check ? e->pad + kPadChanged : nullptr;
     p.converged = e->opts.check_every > 0 ? e->pad + kPadConverged : nullptr;
+#ifdef B2C_DEBUG
+    p.dbg_src_lo = e->alloc[src_i];
+    p.dbg_src_hi = e->alloc[src_i] + e->alloc_bytes;
+    p.dbg_dst_lo = e->alloc[src_i ^ 1];
+    p.dbg_dst_hi = e->alloc[src_i ^ 1] + e->alloc_bytes;
+    p.dbg_peer_before = (long long)kFrameRows * e->pitch + kLeftPad;
+    p.dbg_peer_after = e->alloc_bytes - p.dbg_peer_before;
+    p.dbg_rank = e->rank;
+#endif
     HaloParams &h = p.halo;
     h.nbw = bp.nbw;
     h.nbe = bp.nbe;
     h.enabled = e->any_nb ? 1 : 0;
     if (!h.enabled) return;
-    h.push = (e->bw % e->SB == 0) ? 1 : 0;
+    h.mode = ps.mode;
+    h.fused = (e->bw % e->SB == 0) ? 1 : 0;
     h.depth = e->F;
-    h.wait_epoch = e->epoch;
-    h.post_epoch = e->epoch + 1;
+    h.epoch = device_epoch ? e->epoch - e->epoch_dev : e->epoch;
+    h.epoch_base = device_epoch ? e->pad + kPadEpoch : nullptr;
     h.flags = e->pad + kPadFlags;
+    h.acks = e->pad + kPadAcks;
     h.counters = e->pad + kPadCounters;
+    h.prof = e->prof ? reinterpret_cast<unsigned long long *>(e->pad + kPadProf) : nullptr;
     h.delay = e->delay;
     const int exp[8] = {bp.nbands, bp.nbands, bp.nbw * bp.nchunks, bp.nbe * bp.nchunks,
                         bp.nbw, bp.nbe, bp.nbw, bp.nbe};
@@ -235,10 +298,11 @@ void fill_pass_params(const b2c_engine *e, int k, bool check, int src_i, PassPar
         h.peer_dst[d] = e->peer_base[src_i ^ 1][d];
         // the neighbour sees our data arriving from the opposite direction
         h.peer_flag[d] = e->peer_pad[d] + kPadFlags + opposite_dir(d) * 32;
+        h.peer_ack[d] = e->peer_pad[d] + kPadAcks + opposite_dir(d) * 32;
     }
 }
 
-void fill_push_params(const b2c_engine *e, int buf_i, bool wait, PushParams &q) {
+void fill_push_params(const b2c_engine *e, int buf_i, bool device_epoch, PushParams &q) {
     memset(&q, 0, sizeof q);
     q.src = e->base[buf_i];
     q.pitch = e->pitch;
@@ -248,10 +312,10 @@ void fill_push_params(const b2c_engine *e, int buf_i, bool wait, PushParams &q) 
     q.depth = e->F;
     q.flags = e->pad + kPadFlags;
     q.counters = e->pad + kPadCounters;
-    q.post_epoch = e->epoch + 1;
-    q.wait_epoch = e->epoch;
-    q.wait_epoch_valid = wait ? 1 : 0;
-    q.converged = nullptr;   // only the per-pass fallback push (enqueue_pass) follows the convergence latch
+    q.post_epoch = (device_epoch ? e->epoch - e->epoch_dev : e->epoch) + 1;
+    q.epoch_base = device_epoch ? e->pad + kPadEpoch : nullptr;
+    q.wait_epoch_valid = 0;   // the pass in front of a push has waited for everything the push needs
+    q.converged = nullptr;    // only the per-pass fallback push (enqueue_pass) follows the convergence latch
     for (int d = 0; d < 8; ++d) {
         if (e->nb[d] < 0) continue;
         q.peer_dst[d] = e->peer_base[buf_i][d];
@@ -259,24 +323,49 @@ void fill_push_params(const b2c_engine *e, int buf_i, bool wait, PushParams &q) 
     }
 }
 
-// Splits `reps` iterations into passes of k in {K, ..., 2, 1}; a pass ends on
-// every multiple of check_every (counted from the start of this run).
+// Splits `reps` iterations into groups of at most F iterations (one halo exchange each; a group
+// also ends on every multiple of check_every, counted from the start of this run) and every group
+// into passes of k in {K, ..., 2, 1}.  Without neighbours there is nothing to exchange and a
+// "group" is just the stretch up to the next check.
 std::vector<Pass> make_passes(const b2c_engine *e, int reps) {
     std::vector<Pass> v;
     const int ce = e->opts.check_every;
     int done = 0;
     while (done < reps) {
-        int limit = reps - done;
-        if (ce > 0) limit = std::min(limit, ce - done % ce);
-        int k = e->K;
-        while (k > limit) k >>= 1;
-        done += k;
-        v.push_back({k, ce > 0 && done % ce == 0, (unsigned)done});
+        int glen = reps - done;
+        if (e->any_nb) glen = std::min(glen, std::max(e->F, 1));
+        if (ce > 0) glen = std::min(glen, ce - done % ce);
+        std::vector<int> ks;
+        for (int left = glen; left > 0;) {
+            int k = e->K;
+            while (k > left) k >>= 1;
+            ks.push_back(k);
+            left -= k;
+        }
+        const int n = (int)ks.size();
+        int ext = glen;
+        for (int j = 0; j < n; ++j) {
+            ext -= ks[j];
+            done += ks[j];
+            Pass ps{};
+            ps.k = ks[j];
+            ps.group_end = j == n - 1;
+            ps.check = ps.group_end && ce > 0 && done % ce == 0;
+            ps.iters_after = (unsigned)done;
+            ps.ext = e->any_nb ? ext : 0;
+            ps.mode = 0;
+            if (e->any_nb) {
+                if (j == 0) ps.mode |= kHaloWaitData;
+                if (n >= 2 && j == n - 2) ps.mode |= kHaloPostAck;
+                if (j == n - 1) ps.mode |= kHaloPush | (n >= 2 ? kHaloWaitAck : 0);
+            }
+            v.push_back(ps);
+        }
     }
     return v;
 }
 
-int enqueue_pass(b2c_engine *e, const Pass &ps, cudaStream_t s) {
+int enqueue_pass(b2c_engine *e, const Pass &ps, bool device_epoch, cudaStream_t s) {
     if (e->kernel == B2C_KERNEL_NAIVE) {
         if (e->any_nb) {  // the naive kernel reads the frame without looking at the flags
             unsigned mask = 0;
@@ -294,22 +383,22 @@ int enqueue_pass(b2c_engine *e, const Pass &ps, cudaStream_t s) {
         }
     } else {
         PassParams p;
-        fill_pass_params(e, ps.k, ps.check, e->cur, p);
+        fill_pass_params(e, ps, e->cur, device_epoch, p);
         if (e->kernel == B2C_KERNEL_TMA)
             CK(launch_stream_tma(e->tma, p, e->cur, ps.k, e->SB, e->CH, ps.check, s));
         else
             CK(launch_stream(p, ps.k, e->SB, e->CH, ps.check, s));
         e->launches++;
-        if (e->any_nb && !p.halo.push) {
+        if (e->any_nb && (ps.mode & kHaloPush) && !p.halo.fused) {
             PushParams q;
-            fill_push_params(e, e->cur ^ 1, false, q);
+            fill_push_params(e, e->cur ^ 1, device_epoch, q);
             if (e->opts.check_every > 0) q.converged = e->pad + kPadConverged;
             CK(launch_halo_push(q, s));
             e->launches++;
         }
     }
     e->cur ^= 1;
-    if (e->any_nb) e->epoch++;
+    if (e->any_nb && ps.group_end) e->epoch++;
     if (ps.check) {
         ConvergeParams c{};
         c.changed = e->pad + kPadChanged;
@@ -328,6 +417,22 @@ int enqueue_pass(b2c_engine *e, const Pass &ps, cudaStream_t s) {
     return B2C_OK;
 }
 
+// After the last pass of a run the device-side epoch word catches up with the host's count.
+int enqueue_epoch_sync(b2c_engine *e, bool device_epoch, cudaStream_t s) {
+    if (!e->any_nb || e->kernel == B2C_KERNEL_NAIVE) { e->epoch_dev = e->epoch; return B2C_OK; }
+    if (device_epoch) {
+        if (e->epoch != e->epoch_dev) {
+            CK(launch_add_u32(e->pad + kPadEpoch, e->epoch - e->epoch_dev, s));
+            e->launches++;
+        }
+    } else {
+        CK(launch_set_u32(e->pad + kPadEpoch, e->epoch, s));
+        e->launches++;
+    }
+    e->epoch_dev = e->epoch;
+    return B2C_OK;
+}
+
 void choose_plan(b2c_engine *e) {
     const b2c_opts &o = e->opts;
     e->kernel = o.kernel == B2C_KERNEL_AUTO ? B2C_KERNEL_STREAM : o.kernel;
@@ -340,6 +445,7 @@ void choose_plan(b2c_engine *e) {
     e->K = K;
     e->F = e->any_nb ? K : 1;
     if (e->kernel == B2C_KERNEL_NAIVE) e->F = 1;
+    e->chunk_rows_fixed = o.chunk_rows > 0;
     int SB = o.strip_bytes;
     if (SB != 4 && SB != 8 && SB != 16) {
         // strip width with the lowest modelled pass time (see plan_cost)
@@ -357,6 +463,22 @@ void choose_plan(b2c_engine *e) {
     e->SB = SB;
     e->F = e->any_nb ? K : 1;
     if (e->kernel == B2C_KERNEL_NAIVE) e->F = 1;
+    if (e->any_nb && e->kernel != B2C_KERNEL_NAIVE) {
+        // Halo depth F = iterations between two exchanges (a multiple of K).  Every handshake with
+        // the neighbours costs microseconds whatever the block size; the price of a deeper halo is
+        // recomputing (F-K)/2 rows and columns of the neighbours' blocks per pass on average.
+        const int cap = std::min(kMaxHaloDepth, std::min(e->R, e->C));
+        int F = K;
+        if (o.halo_depth > 0) {
+            F = std::max(K, std::min(o.halo_depth, cap) / K * K);
+        } else {
+            for (int m = 8; m >= 2; m >>= 1) {
+                const double extra = 0.5 * (m - 1) * K * (2.0 / e->R + 2.0 / e->C);
+                if (m * K <= cap && extra <= 0.02) { F = m * K; break; }
+            }
+        }
+        e->F = F;
+    }
     // the byte-per-thread kernel has no change detector: a check would always report "unchanged"
     if (e->kernel == B2C_KERNEL_NAIVE || e->kernel == B2C_KERNEL_RESIDENT) e->opts.check_every = 0;
 }
@@ -371,9 +493,10 @@ int autotune_chunk_rows(b2c_engine *e) {
     static const bool off = getenv("B200CONV_AUTOTUNE") && atoi(getenv("B200CONV_AUTOTUNE")) == 0;
     if (off || e->opts.chunk_rows > 0) return B2C_OK;
     if (e->kernel != B2C_KERNEL_STREAM && e->kernel != B2C_KERNEL_TMA) return B2C_OK;
-    // Multi-rank blocks keep the modelled plan: what is timed here runs without neighbours, and
-    // measured on 4 and 8 GPUs the halo-free optimum (longer chunks) is up to 20 % slower once
-    // ring warps have to finish their chunk before a neighbour's next pass may start.
+    // Multi-rank blocks are tuned together with their neighbours once the peers are connected
+    // (b2c_engine_tune_*): what is timed here runs without neighbours, and measured on 4 and 8 GPUs
+    // the halo-free optimum (longer chunks) is up to 20 % slower once ring warps have to finish their
+    // chunk before a neighbour's next pass may start.
     if (e->P * e->Q > 1) return B2C_OK;
     const double bytes = (double)e->bw * e->R;
     if (bytes < 1e6) return B2C_OK;   // tiny images: a pass is shorter than the launch path, keep the model
@@ -401,9 +524,11 @@ int autotune_chunk_rows(b2c_engine *e) {
             if (c < 64 && bytes >= 256e6) continue;                       // pointless on large blocks
             if (c > 48 && bytes < 16e6) continue;                         // and long chunks starve small ones
             e->opts.chunk_rows = c;
-            for (bool &ok : e->plan_ok) ok = false;
+            e->plan_cache.clear();
             PassParams p;
-            fill_pass_params(e, e->K, false, 0, p);
+            Pass ps{};
+            ps.k = e->K;
+            fill_pass_params(e, ps, 0, false, p);
             cudaError_t ce = cudaSuccess;
             const int reps = bytes < 16e6 ? 41 : (bytes < 128e6 ? 9 : 3);   // short passes: average more of them
             for (int it = 0; it < reps && ce == cudaSuccess; ++it) {
@@ -428,7 +553,7 @@ int autotune_chunk_rows(b2c_engine *e) {
     if (s) cudaStreamDestroy(s);
     e->any_nb = any_nb;
     e->opts.chunk_rows = best;   // 0 (model) when nothing was timed
-    for (bool &ok : e->plan_ok) ok = false;
+    e->plan_cache.clear();
     return rc;
 }
 
@@ -441,7 +566,7 @@ int alloc_buffers(b2c_engine *e) {
             CK(cudaMemset(b, 0, (size_t)e->cbytes + 64));
         }
     } else {
-        e->pitch = round_up(kLeftPad + (long long)e->bw + 32 + 16, 128);
+        e->pitch = round_up(kLeftPad + (long long)e->bw + kRightPad, 128);
         e->alloc_bytes = e->pitch * (e->R + 2 * kFrameRows) + 1024;  // tail slack: last band's window
         for (int i = 0; i < 2; ++i) {
             CK(cudaMalloc(&e->alloc[i], (size_t)e->alloc_bytes));
@@ -465,6 +590,7 @@ void b2c_default_opts(b2c_opts *o) {
     o->filter = B2C_GAUSSIAN;
     o->kernel = B2C_KERNEL_AUTO;
     o->use_graph = -1;
+    o->halo_depth = 0;
 }
 
 b2c_engine *b2c_engine_create(int device, int W, int H, int CH, int P, int Q, int rank, const b2c_opts *opts) {
@@ -511,6 +637,7 @@ b2c_engine *b2c_engine_create(int device, int W, int H, int CH, int P, int Q, in
         return nullptr;
     }
     e->sm_count = smc;
+    e->prof = getenv("B200CONV_HALO_PROF") && atoi(getenv("B200CONV_HALO_PROF")) != 0;
     choose_plan(e);
     if (alloc_buffers(e) != B2C_OK) {
         b2c_engine_destroy(e);
@@ -660,6 +787,7 @@ int b2c_engine_import(b2c_engine *e, const void *blobs, int n) {
         e->peer_pad[d] = e->rank_pad[k];
     }
     e->connected = true;
+    drop_graphs(e);
     return B2C_OK;
 }
 
@@ -667,6 +795,7 @@ int b2c_engine_disconnect(b2c_engine *e) {
     if (!e) return B2C_EINVAL;
     CK(cudaSetDevice(e->device));
     CK(cudaDeviceSynchronize());
+    drop_graphs(e);
     for (void *p : e->ipc_opened) cudaIpcCloseMemHandle(p);
     e->ipc_opened.clear();
     memset(e->peer_base, 0, sizeof e->peer_base);
@@ -705,6 +834,7 @@ int b2c_engine_connect_local(b2c_engine **engines, int n) {
             e->peer_pad[d] = engines[k]->pad;
         }
         e->connected = true;
+        drop_graphs(e);
     }
     return B2C_OK;
 }
@@ -768,9 +898,11 @@ int b2c_engine_exchange(b2c_engine *e, void *stream) {
     CK(cudaSetDevice(e->device));
     PushParams q;
     fill_push_params(e, e->cur, false, q);
+    q.epoch_word = e->pad + kPadEpoch;   // the device-side epoch follows (block (0,0) stores post_epoch)
     CK(launch_halo_push(q, (cudaStream_t)stream));
     e->launches++;
     e->epoch++;
+    e->epoch_dev = e->epoch;
     return B2C_OK;
 }
 
@@ -829,6 +961,11 @@ int b2c_engine_run(b2c_engine *e, int reps, void *stream) {
     }
     const std::vector<Pass> passes = make_passes(e, reps);
     e->iters_done = reps;
+    // Epochs come from a device word plus a per-pass offset, so a run is the same sequence of
+    // launches every time and can be replayed as a CUDA graph — with neighbours too.  Only the
+    // convergence check (whose latch rewinds the epoch) and the byte-per-thread kernel bake
+    // absolute epochs into the parameters.
+    const bool device_epoch = e->opts.check_every == 0 && e->kernel != B2C_KERNEL_NAIVE;
     if (e->opts.check_every > 0) {
         CK(cudaMemsetAsync(e->pad + kPadConverged, 0, 2 * sizeof(uint32_t), s));
         e->last_passes = passes;
@@ -837,7 +974,7 @@ int b2c_engine_run(b2c_engine *e, int reps, void *stream) {
         e->pending_converge_fixup = true;
     }
     bool graph = e->opts.use_graph == 1 || (e->opts.use_graph < 0 && passes.size() >= 8);
-    if (e->any_nb || e->opts.check_every > 0 || s == nullptr) graph = false;  // epochs are baked into params
+    if (!device_epoch || s == nullptr) graph = false;
     if (graph) {  // a caller that is capturing this stream itself gets plain launches into its graph
         cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
         if (cudaStreamIsCapturing(s, &cs) != cudaSuccess || cs != cudaStreamCaptureStatusNone) {
@@ -848,20 +985,20 @@ int b2c_engine_run(b2c_engine *e, int reps, void *stream) {
     if (graph) {
         const auto key = std::make_pair(reps, e->cur);
         auto it = e->graphs.find(key);
+        const uint32_t epoch0 = e->epoch;
         if (it == e->graphs.end()) {
-            if (e->graphs.size() >= 16) {  // callers that vary `reps` endlessly must not hoard graphs
-                for (auto &g : e->graphs) cudaGraphExecDestroy(g.second);
-                e->graphs.clear();
-            }
+            if (e->graphs.size() >= 16) drop_graphs(e);  // callers that vary `reps` endlessly must not hoard graphs
             const int cur0 = e->cur;
             const long long l0 = e->launches, g0 = total_launches();
             cudaGraph_t g;
             CK(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
             int rc = B2C_OK;
             for (const Pass &ps : passes)
-                if ((rc = enqueue_pass(e, ps, s)) != B2C_OK) break;
+                if ((rc = enqueue_pass(e, ps, true, s)) != B2C_OK) break;
+            if (rc == B2C_OK) rc = enqueue_epoch_sync(e, true, s);
             cudaError_t ce = cudaStreamEndCapture(s, &g);
             e->cur = cur0;
+            e->epoch = e->epoch_dev = epoch0;
             e->launches = l0;
             count_launch(g0 - total_launches());  // captured, not launched
             if (rc != B2C_OK) {
@@ -876,16 +1013,56 @@ int b2c_engine_run(b2c_engine *e, int reps, void *stream) {
             it = e->graphs.emplace(key, ge).first;
         }
         CK(cudaGraphLaunch(it->second, s));
-        e->launches += (long long)passes.size();
-        count_launch((long long)passes.size());
+        e->launches += 1;   // one host launch; the graph's kernel nodes are counted by count_launch
+        long long nodes = (long long)passes.size();
+        uint32_t groups = 0;
+        for (const Pass &ps : passes) {
+            if (e->any_nb && ps.group_end) groups++;
+            if (e->any_nb && (ps.mode & kHaloPush) && e->bw % e->SB != 0) nodes++;
+        }
+        if (groups) nodes++;
+        count_launch(nodes);
         e->cur ^= (int)(passes.size() & 1);
+        e->epoch = e->epoch_dev = epoch0 + groups;
         return B2C_OK;
     }
     for (const Pass &ps : passes) {
-        int rc = enqueue_pass(e, ps, s);
+        int rc = enqueue_pass(e, ps, device_epoch, s);
         if (rc != B2C_OK) return rc;
     }
-    return B2C_OK;
+    return enqueue_epoch_sync(e, device_epoch, s);
+}
+
+// Pass-by-pass variant of b2c_engine_run for callers that interleave several engines on ONE
+// device (the sequential multi-rank emulation of the tests): plan_run fixes the pass list,
+// run_pass enqueues pass i.  Every rank must have enqueued pass i before any rank enqueues
+// pass i+1 — then every flag a kernel waits for is already set when it starts.
+int b2c_engine_plan_run(b2c_engine *e, int reps) {
+    if (!e || reps < 0) return B2C_EINVAL;
+    if (settle(e) != B2C_OK) return B2C_ECUDA;
+    if (e->opts.boundary == B2C_CUDA_COMPAT || e->kernel == B2C_KERNEL_RESIDENT || e->opts.check_every > 0) {
+        set_error("engine_plan_run: streaming kernels without check_every only");
+        return B2C_EINVAL;
+    }
+    if (e->any_nb && (!e->connected || e->epoch == 0)) {
+        set_error("engine_plan_run: connect the peers and call b2c_engine_exchange first");
+        return B2C_EINVAL;
+    }
+    e->staged = make_passes(e, reps);
+    e->iters_done = reps;
+    return (int)e->staged.size();
+}
+
+int b2c_engine_run_pass(b2c_engine *e, int i, void *stream) {
+    if (!e || i < 0 || i >= (int)e->staged.size()) return B2C_EINVAL;
+    CK(cudaSetDevice(e->device));
+    const bool device_epoch = e->kernel != B2C_KERNEL_NAIVE;
+    int rc = enqueue_pass(e, e->staged[(size_t)i], device_epoch, (cudaStream_t)stream);
+    if (rc == B2C_OK && i + 1 == (int)e->staged.size()) {
+        rc = enqueue_epoch_sync(e, device_epoch, (cudaStream_t)stream);
+        e->staged.clear();
+    }
+    return rc;
 }
 
 int b2c_engine_iterations_done(b2c_engine *e) {
@@ -911,12 +1088,13 @@ int b2c_engine_iterations_done(b2c_engine *e) {
             uint32_t ep = e->run_epoch0;
             for (const Pass &ps : e->last_passes) {
                 cur ^= 1;
-                if (e->any_nb) ep++;
-                if (ps.iters_after >= v[1]) break;
+                if (e->any_nb && ps.group_end) ep++;
+                if (ps.iters_after >= v[1]) break;   // a check pass ends its group
             }
             e->cur = cur;
-            e->epoch = ep;
+            e->epoch = e->epoch_dev = ep;
             e->iters_done = (int)v[1];
+            if (e->any_nb) CK(cudaMemcpy(e->pad + kPadEpoch, &ep, sizeof ep, cudaMemcpyHostToDevice));
         }
     }
     return e->iters_done;
@@ -937,7 +1115,7 @@ int b2c_engine_describe(const b2c_engine *e, char *buf, size_t buflen) {
                  e->bw);
         return B2C_OK;
     }
-    const BandPlan bp = make_band_plan(e, e->K);
+    const BandPlan bp = make_band_plan(e, e->K, 0);
     snprintf(buf, buflen,
              "kernel=%s tb=%d strip=%dB block=%dx%d(bytes %d) pitch=%lld bands=%d(valid %dB) chunks=%d(x%d rows) "
              "warps=%d halo_depth=%d fused_push=%d grid=%dx%d rank=%d",
@@ -966,15 +1144,158 @@ int b2c_debug_band_plan(int rows, int cols, int channels, int has_neighbours, in
     for (int &n : e.nb) n = has_neighbours ? 0 : -1;
     e.sm_count = sm_count > 0 ? sm_count : 148;
     choose_plan(&e);
-    const BandPlan bp = make_band_plan(&e, e.K);
+    const BandPlan bp = make_band_plan(&e, e.K, 0);
     const int v[10] = {bp.hlo, bp.vw, bp.nbands, bp.nchunks, bp.chunk_rows, bp.nbw, bp.nbe, e.K, e.SB, e.F};
     memcpy(out, v, sizeof v);
+    return B2C_OK;
+}
+
+// Test hook (host only): the pass list of a run and each pass's plan, for the CPU property tests of
+// the grouped halo exchange.  Per pass 12 ints: {k, ext, mode, group_end, rows, row_bytes, nbands,
+// nchunks, chunk_rows, last_chunk_rows, nbw, nbe}.  Returns the number of passes (at most max_passes
+// are written) or a negative code.  A rank with neighbours on all eight sides is modelled.
+int b2c_debug_pass_plans(int rows, int cols, int channels, int has_neighbours, int tb, int strip_bytes, int chunk_rows,
+                         int halo_depth, int reps, int sm_count, int *out, int max_passes) {
+    if (rows <= 0 || cols <= 0 || (channels != 1 && channels != 3) || reps < 0 || !out) return B2C_EINVAL;
+    if ((long long)cols * channels > (1ll << 30)) return B2C_ETOOBIG;
+    b2c_engine e;
+    b2c_default_opts(&e.opts);
+    e.opts.tb = tb;
+    e.opts.strip_bytes = strip_bytes;
+    e.opts.chunk_rows = chunk_rows;
+    e.opts.halo_depth = halo_depth;
+    e.R = rows, e.C = cols, e.CH = channels, e.bw = cols * channels;
+    e.W = cols, e.H = rows;
+    e.any_nb = has_neighbours != 0;
+    for (int &n : e.nb) n = has_neighbours ? 0 : -1;
+    e.sm_count = sm_count > 0 ? sm_count : 148;
+    choose_plan(&e);
+    const std::vector<Pass> passes = make_passes(&e, reps);
+    int n = 0;
+    for (const Pass &ps : passes) {
+        if (n < max_passes) {
+            const BandPlan bp = make_band_plan(&e, ps.k, ps.ext);
+            const int v[12] = {ps.k, ps.ext, ps.mode, ps.group_end ? 1 : 0, bp.rows, bp.bw, bp.nbands, bp.nchunks,
+                               bp.chunk_rows, bp.rows - (bp.nchunks - 1) * bp.chunk_rows, bp.nbw, bp.nbe};
+            memcpy(out + 12 * n, v, sizeof v);
+        }
+        ++n;
+    }
+    return n;
+}
+
+// ---- coupled tuning of rows-per-warp (collective: every rank makes the same calls in the same order)
+
+static const int kTuneCand[] = {24, 32, 40, 48, 56, 64, 80, 96, 112, 128, 160, 192};
+
+static int tune_candidate(const b2c_engine *e, int i) {
+    int n = 0;
+    const int lo = min_edge_chunk(e, e->K);
+    for (int c : kTuneCand) {
+        if (c < lo || 2 * c > e->R) continue;
+        if (n == i) return c;
+        ++n;
+    }
+    return i < 0 ? n : 0;
+}
+
+int b2c_engine_tune_count(const b2c_engine *e) {
+    if (!e) return B2C_EINVAL;
+    static const bool off = getenv("B200CONV_AUTOTUNE") && atoi(getenv("B200CONV_AUTOTUNE")) == 0;
+    if (off || e->chunk_rows_fixed || e->P * e->Q == 1 || !e->any_nb) return 0;
+    if (e->kernel != B2C_KERNEL_STREAM && e->kernel != B2C_KERNEL_TMA) return 0;
+    if ((double)e->bw * e->R < 4e6) return 0;   // a pass is shorter than a handshake: keep the model
+    return tune_candidate(e, -1);
+}
+
+// Times candidate i with the halo exchange live: a fresh exchange, one untimed stretch, one timed
+// stretch of the iteration loop on whatever the buffers hold (kernel time does not depend on pixel
+// values).  Returns milliseconds on this rank; the caller reduces with MAX over the ranks.
+double b2c_engine_tune_time(b2c_engine *e, int i, void *stream) {
+    if (!e || tune_candidate(e, i) <= 0 || !e->connected) return -1.0;
+    if (cudaSetDevice(e->device) != cudaSuccess) return -1.0;
+    cudaStream_t s = (cudaStream_t)stream;
+    e->opts.chunk_rows = tune_candidate(e, i);
+    e->plan_cache.clear();
+    drop_graphs(e);
+    const int ug = e->opts.use_graph;
+    e->opts.use_graph = 0;
+    const int reps = 8 * std::max(e->F, e->K);
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    float ms = -1.f;
+    if (cudaEventCreate(&ev0) == cudaSuccess && cudaEventCreate(&ev1) == cudaSuccess &&
+        b2c_engine_exchange(e, stream) == B2C_OK && b2c_engine_run(e, reps, stream) == B2C_OK &&
+        cudaEventRecord(ev0, s) == cudaSuccess && b2c_engine_run(e, reps, stream) == B2C_OK &&
+        cudaEventRecord(ev1, s) == cudaSuccess && cudaEventSynchronize(ev1) == cudaSuccess)
+        cudaEventElapsedTime(&ms, ev0, ev1);
+    else
+        set_error("engine_tune_time: %s", cudaGetErrorString(cudaGetLastError()));
+    if (ev0) cudaEventDestroy(ev0);
+    if (ev1) cudaEventDestroy(ev1);
+    e->opts.use_graph = ug;
+    return ms;
+}
+
+int b2c_engine_tune_set(b2c_engine *e, int i) {
+    if (!e) return B2C_EINVAL;
+    e->opts.chunk_rows = i >= 0 ? tune_candidate(e, i) : 0;   // 0 = the modelled plan
+    e->plan_cache.clear();
+    drop_graphs(e);
+    return B2C_OK;
+}
+
+// ---- device-side start barrier and wait-time counters
+
+int b2c_engine_barrier(b2c_engine *e, void *stream) {
+    if (!e) return B2C_EINVAL;
+    const int n = e->P * e->Q;
+    if (n == 1) return B2C_OK;
+    if (!e->connected) {
+        set_error("engine_barrier: peers are not connected");
+        return B2C_EINVAL;
+    }
+    CK(cudaSetDevice(e->device));
+    BarrierParams b{};
+    b.slots = e->pad + kPadBarrier;
+    for (int k = 0; k < n; ++k) b.peer_slots[k] = e->rank_pad[k] + kPadBarrier;
+    b.nranks = n;
+    b.rank = e->rank;
+    b.seq = ++e->barrier_seq;
+    b.skew_cycles = reinterpret_cast<unsigned long long *>(e->pad + kPadBarrierSkew);
+    CK(launch_barrier(b, (cudaStream_t)stream));
+    e->launches++;
+    return B2C_OK;
+}
+
+int64_t b2c_engine_barrier_wait_cycles(b2c_engine *e) {
+    if (!e) return B2C_EINVAL;
+    CK(cudaSetDevice(e->device));
+    CK(cudaDeviceSynchronize());
+    unsigned long long v = 0;
+    CK(cudaMemcpy(&v, e->pad + kPadBarrierSkew, sizeof v, cudaMemcpyDeviceToHost));
+    return (int64_t)v;
+}
+
+int b2c_engine_set_profile(b2c_engine *e, int on) {
+    if (!e) return B2C_EINVAL;
+    e->prof = on != 0;
+    drop_graphs(e);
+    return B2C_OK;
+}
+
+int b2c_engine_halo_profile(b2c_engine *e, uint64_t out[40], int reset) {
+    if (!e || !out) return B2C_EINVAL;
+    CK(cudaSetDevice(e->device));
+    CK(cudaDeviceSynchronize());
+    CK(cudaMemcpy(out, e->pad + kPadProf, kProfWords64 * sizeof(uint64_t), cudaMemcpyDeviceToHost));
+    if (reset) CK(cudaMemset(e->pad + kPadProf, 0, kProfWords64 * sizeof(uint64_t)));
     return B2C_OK;
 }
 
 int b2c_engine_set_delay(b2c_engine *e, int64_t cycles) {
     if (!e) return B2C_EINVAL;
     e->delay = cycles;
+    drop_graphs(e);   // the delay is a kernel parameter
     return B2C_OK;
 }
 
@@ -1099,7 +1420,7 @@ extern "C" int b2c_blur_device_noalloc(const uint8_t *d_in, int64_t in_pitch, ui
     CK(cudaDeviceGetAttribute(&e.sm_count, cudaDevAttrMultiProcessorCount, dev));
     choose_plan(&e);
 
-    e.pitch = round_up(kLeftPad + (long long)e.bw + 32 + 16, 128);
+    e.pitch = round_up(kLeftPad + (long long)e.bw + kRightPad, 128);
     e.alloc_bytes = round_up(e.pitch * (e.R + 2 * kFrameRows) + 1024, 256);
     const long long pad_bytes = kPadWords * (long long)sizeof(uint32_t);
     const long long need = 2 * e.alloc_bytes + pad_bytes;
@@ -1139,7 +1460,7 @@ extern "C" int b2c_blur_device_noalloc(const uint8_t *d_in, int64_t in_pitch, ui
         e.epoch++;
     }
     for (const Pass &ps : make_passes(&e, reps)) {
-        rc = enqueue_pass(&e, ps, s);
+        rc = enqueue_pass(&e, ps, false, s);   // absolute epochs: nothing is replayed
         if (rc != B2C_OK) return rc;
     }
     CK(cudaMemcpy2DAsync(d_out, (size_t)out_pitch, e.base[e.cur], (size_t)e.pitch, (size_t)e.bw, (size_t)e.R,

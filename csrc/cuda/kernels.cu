@@ -168,14 +168,16 @@ cudaError_t launch_compat(const uint8_t *src, uint8_t *dst, int W, int H, int ch
 // assumptions), then the last CTA of a direction publishes the epoch.
 __global__ void halo_push_kernel(const PushParams q) {
     const int d = blockIdx.y;
-    if (!q.peer_dst[d]) return;
     // After the convergence latch every pass is skipped on every rank; the ring pushes that
     // follow them must be skipped too or they would publish epochs nobody computed.
     if (q.converged && *q.converged) return;
+    const uint32_t base = q.epoch_base ? __ldcg(q.epoch_base) : 0u;
+    if (q.epoch_word && blockIdx.x == 0 && d == 0 && threadIdx.x == 0) *q.epoch_word = q.post_epoch;
+    if (!q.peer_dst[d]) return;
     if (q.wait_epoch_valid && threadIdx.x == 0) {
         // Do not overwrite a frame the neighbour may still be reading.
         const long long t0 = clock64();
-        while ((int)(ld_acquire_sys(q.flags + d * 32) - q.wait_epoch) < 0) {
+        while ((int)(ld_acquire_sys(q.flags + d * 32) - (q.wait_epoch + base)) < 0) {
             if (clock64() - t0 > (20ll << 30)) {
                 printf("b200conv: halo push wait timeout dir=%d want=%u\n", d, q.wait_epoch);
                 __trap();
@@ -211,7 +213,7 @@ __global__ void halo_push_kernel(const PushParams q) {
         if (old + 1 == gridDim.x) {
             q.counters[d * 32] = 0;
             __threadfence_system();
-            st_release_sys(q.peer_flag[d], q.post_epoch);
+            st_release_sys(q.peer_flag[d], q.post_epoch + base);
         }
     }
 }
@@ -261,21 +263,24 @@ __global__ void set_u32_kernel(unsigned int *p, unsigned int v) { *p = v; }
 // every rank's tag s+1, and a rank publishes s+1 after it finished reading s,
 // so two sets are enough.  (Found with the host model, csrc/core/halo_emul.cpp.)
 __global__ void converge_kernel(const ConvergeParams c) {
-    if (threadIdx.x != 0 || blockIdx.x != 0) return;
-    const unsigned mine = *c.changed;
-    *c.changed = 0;
+    // One warp: lane k (+32) talks to rank k, so the N stores and the N polls each go out together
+    // instead of one system-scope round trip after the other.
+    const int lane = threadIdx.x;
+    unsigned mine = 0;
+    if (lane == 0) {
+        mine = *c.changed;
+        *c.changed = 0;
+    }
+    mine = __shfl_sync(kFull, mine, 0);
     // slot value = 2*seq + bit so that a slot from an older check never matches
     const unsigned tag = c.seq * 2u;
     const int set = (int)(c.seq & 1u) * kMaxRanks;
-    for (int k = 0; k < c.nranks; ++k) {
-        __threadfence_system();
-        st_release_sys(c.peer_slots[k] + set + c.rank, tag | (mine ? 1u : 0u));
-    }
+    for (int k = lane; k < c.nranks; k += 32) st_release_sys(c.peer_slots[k] + set + c.rank, tag | (mine ? 1u : 0u));
     unsigned any = 0;
-    for (int k = 0; k < c.nranks; ++k) {
+    for (int k = lane; k < c.nranks; k += 32) {
         const long long t0 = clock64();
         unsigned v;
-        while (((v = ld_acquire_sys(c.slots + set + k)) & ~1u) != tag) {
+        while (((v = ld_relaxed_sys(c.slots + set + k)) & ~1u) != tag) {
             if (clock64() - t0 > (20ll << 30)) {
                 printf("b200conv: convergence wait timeout rank=%d peer=%d\n", c.rank, k);
                 __trap();
@@ -283,20 +288,55 @@ __global__ void converge_kernel(const ConvergeParams c) {
         }
         any |= v & 1u;
     }
-    if (!any && !*c.converged) {
+    any = __any_sync(kFull, any != 0);
+    if (lane == 0 && !any && !*c.converged) {
         *c.converged = 1;
         *c.converged_at = c.iters_after;
     }
 }
 
 cudaError_t launch_converge(const ConvergeParams &c, cudaStream_t s) {
-    converge_kernel<<<1, 32, 0, s>>>(c);
+    converge_kernel<<<1, 32, 0, s>>>(c);   // exactly one warp
     count_launch(1);
     return cudaGetLastError();
 }
 
 cudaError_t launch_set_u32(unsigned int *p, unsigned int v, cudaStream_t s) {
     set_u32_kernel<<<1, 1, 0, s>>>(p, v);
+    count_launch(1);
+    return cudaGetLastError();
+}
+
+__global__ void add_u32_kernel(unsigned int *p, unsigned int v) { *p += v; }
+
+cudaError_t launch_add_u32(unsigned int *p, unsigned int v, cudaStream_t s) {
+    add_u32_kernel<<<1, 1, 0, s>>>(p, v);
+    count_launch(1);
+    return cudaGetLastError();
+}
+
+// Start barrier on the device (replaces MPI_Barrier in front of the timer, mpi_convolution.c:151):
+// lane k (+32) stores the sequence number into rank k's array and polls word k of its own, so a
+// rank's stream passes this kernel within a few microseconds of the last rank reaching it.
+__global__ void barrier_kernel(const BarrierParams b) {
+    const int lane = threadIdx.x;
+    const long long t0 = clock64();
+    for (int k = lane; k < b.nranks; k += 32) st_release_sys(b.peer_slots[k] + b.rank, b.seq);
+    for (int k = lane; k < b.nranks; k += 32) {
+        while ((int)(ld_relaxed_sys(b.slots + k) - b.seq) < 0) {
+            if (clock64() - t0 > (20ll << 30)) {
+                printf("b200conv: start barrier timeout rank=%d peer=%d\n", b.rank, k);
+                __trap();
+            }
+        }
+        (void)ld_acquire_sys(b.slots + k);
+    }
+    __syncwarp();
+    if (lane == 0 && b.skew_cycles) *b.skew_cycles = (unsigned long long)(clock64() - t0);
+}
+
+cudaError_t launch_barrier(const BarrierParams &b, cudaStream_t s) {
+    barrier_kernel<<<1, 32, 0, s>>>(b);
     count_launch(1);
     return cudaGetLastError();
 }

@@ -22,9 +22,11 @@ struct PushParams {
     uint32_t *peer_flag[8];
     uint32_t *flags;
     uint32_t *counters;
-    uint32_t post_epoch;
+    uint32_t post_epoch;     // published value, relative to *epoch_base when that is set
     uint32_t wait_epoch;
     int wait_epoch_valid;
+    const uint32_t *epoch_base;      // device word holding the epoch at the start of the run (null: 0)
+    uint32_t *epoch_word;            // when set, block (0,0) stores post_epoch there (initial exchange)
     const unsigned int *converged;   // when set and non-zero the push is skipped (like the passes)
 };
 
@@ -54,6 +56,17 @@ cudaError_t launch_halo_push(const PushParams &q, cudaStream_t s);
 cudaError_t launch_halo_wait(const uint32_t *flags, unsigned mask, uint32_t epoch, cudaStream_t s);
 cudaError_t launch_converge(const ConvergeParams &c, cudaStream_t s);
 cudaError_t launch_set_u32(unsigned int *p, unsigned int v, cudaStream_t s);
+cudaError_t launch_add_u32(unsigned int *p, unsigned int v, cudaStream_t s);
+// Device-side start barrier over peer memory: every rank stores `seq` into its word of every
+// rank's slot array and spins until all words of its own array carry `seq`.
+struct BarrierParams {
+    uint32_t *slots;                  // our array: kMaxRanks words
+    uint32_t *peer_slots[kMaxRanks];  // every rank's array (index = rank)
+    int nranks, rank;
+    uint32_t seq;
+    unsigned long long *skew_cycles;  // optional: cycles this rank spent waiting (written by lane 0)
+};
+cudaError_t launch_barrier(const BarrierParams &b, cudaStream_t s);
 
 long long total_launches();
 void count_launch(long long n);

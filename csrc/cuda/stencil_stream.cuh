@@ -34,25 +34,44 @@
 
 namespace b2c {
 
-constexpr int kFrameRows = 12;  // halo frame rows above/below the block: max K (8) + the 3x loop overrun + slack
-constexpr int kLeftPad = 32;    // frame bytes left of the block, 16B multiple >= 8*3
+constexpr int kMaxHaloDepth = 32;  // deepest halo F a rank may keep (iterations between two exchanges)
+constexpr int kFrameRows = 40;  // halo frame rows above/below the block: max F (32) + the 3x loop overrun + slack
+constexpr int kLeftPad = 128;   // frame bytes left of the block: round_up(F*3, 16) + the widest window overhang (32)
+constexpr int kRightPad = 128;  // frame bytes right of the block (before rounding the pitch up to 128)
 constexpr int kWarpsPerCta = 4;
 #ifndef B2C_MIN_CTAS
 #define B2C_MIN_CTAS 4   // resident CTAs per SM the register allocator must allow (<= 128 regs/thread)
 #endif
 constexpr unsigned kFull = 0xffffffffu;
 
+// What a pass does with its neighbours.  A rank keeps an F-deep halo and exchanges it once per
+// *group* of passes (F iterations): the first pass of a group waits for the neighbours' rings, the
+// passes in between recompute the shrinking part of the halo themselves (their block is extended
+// into the frame), the last pass pushes the new F-deep ring.  Because the in-between passes write
+// the frames of both buffers, a pusher must also know that the neighbour is done with the frame it
+// is about to overwrite: the readers of the second-to-last pass post an "ack" epoch for that.
+enum : int {
+    kHaloWaitData = 1,  // ring warps wait for the neighbours' data epoch before reading a frame
+    kHaloPostAck = 2,   // ring warps count in and publish the ack epoch (no stores)
+    kHaloWaitAck = 4,   // ring warps wait for the neighbours' ack epoch before pushing
+    kHaloPush = 8,      // ring warps store their ring into the neighbours' frames and publish the data epoch
+};
+
 struct HaloParams {
     int enabled;            // any neighbour at all
-    int push;               // 1: push ring from this kernel (aligned fast path)
+    int mode;               // kHalo* bits of this pass
+    int fused;              // 1: kHaloPush stores come from this kernel (aligned widths); 0: halo_push_kernel follows
     int depth;              // ring depth F (rows, and F*CH byte columns)
-    uint32_t wait_epoch;    // flags must be >= this before touching a frame
-    uint32_t post_epoch;    // value published after the pushes
+    uint32_t epoch;         // group epoch E, relative to *epoch_base: data/ack flags must be >= E, E+1 is published
+    const uint32_t *epoch_base;  // device word holding the epoch at the start of the run (null: 0)
     uint8_t *peer_dst[8];   // neighbour's destination buffer, interior origin (or null)
-    uint32_t *peer_flag[8]; // neighbour's flag word that *we* write for direction d
-    uint32_t *flags;        // our flag words, index = direction the data came from
+    uint32_t *peer_flag[8]; // neighbour's data-flag word that *we* write for direction d
+    uint32_t *peer_ack[8];  // neighbour's ack word that *we* write for direction d
+    uint32_t *flags;        // our data-flag words, index = direction the data came from
+    uint32_t *acks;         // our ack words, index = direction of the neighbour that acknowledged
     uint32_t *counters;     // our per-direction arrival counters
-    int expected[8];        // pusher warps per direction
+    unsigned long long *prof;  // opt-in wait/publish cycle counters (null: off), layout in engine.cu
+    int expected[8];        // ring warps per direction
     int nbw, nbe;           // bands holding the west / east ring
     long long delay;        // test hook: spin this many clocks before each wait
 };
@@ -69,8 +88,32 @@ struct PassParams {
     int zero_n, zero_s, zero_w, zero_e;  // outside that side is outside the image (ZERO mode)
     unsigned int *changed;  // CHECK: OR-accumulated "last stage changed a byte"
     const unsigned int *converged;  // when set (non-null and non-zero) the pass is skipped
+    int org_x, org_y;       // position of src/dst (0,0) inside the allocation (bytes, rows): TMA coordinates
+#ifdef B2C_DEBUG
+    const uint8_t *dbg_src_lo, *dbg_src_hi;   // [lo, hi) of the source / destination allocation
+    uint8_t *dbg_dst_lo, *dbg_dst_hi;
+    long long dbg_peer_before, dbg_peer_after;  // bytes of a peer allocation before / after its interior origin
+    int dbg_rank;
+#endif
     HaloParams halo;
 };
+
+#ifdef B2C_DEBUG
+// Debug build (python build.py --debug): every global address the streaming kernels form is checked
+// against the allocation it must fall into, epochs are checked for monotonicity; a violation prints
+// rank / what / address and traps.  Stands in for compute-sanitizer where that tool is not available.
+__device__ __noinline__ void dbg_fail(const char *what, int rank, const void *p, const void *lo, const void *hi) {
+    printf("b200conv DEBUG: rank %d: %s address %p outside [%p, %p)\n", rank, what, p, lo, hi);
+    __trap();
+}
+#define B2C_DBG_RANGE(what, rank, ptr, nbytes, lo, hi)                                              \
+    do {                                                                                            \
+        if ((const uint8_t *)(ptr) < (const uint8_t *)(lo) || (const uint8_t *)(ptr) + (nbytes) > (const uint8_t *)(hi)) \
+            b2c::dbg_fail(what, rank, ptr, lo, hi);                                                 \
+    } while (0)
+#else
+#define B2C_DBG_RANGE(what, rank, ptr, nbytes, lo, hi) do { } while (0)
+#endif
 
 __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t *p) {
     uint32_t v;
@@ -79,6 +122,13 @@ __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t *p) {
 }
 __device__ __forceinline__ void st_release_sys(uint32_t *p, uint32_t v) {
     asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+// Poll without the L1 invalidate an acquire load drags along; one ld_acquire_sys after the value
+// has shown up gives the ordering.
+__device__ __forceinline__ uint32_t ld_relaxed_sys(const uint32_t *p) {
+    uint32_t v;
+    asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
 }
 
 // Streaming loads/stores: L2 only, nothing is reused from L1.
@@ -177,7 +227,7 @@ __device__ __forceinline__ void stream_band(const PassParams &p, Feed &feed, con
     const int x0 = band * p.vw - p.hlo;      // window start, block-local byte column
     const int xs = x0 + lane * SB;           // this lane's strip
     const int out_r0 = chunk * p.chunk_rows;
-    const int out_r1 = min(out_r0 + p.chunk_rows, p.rows);
+    const int out_r1 = chunk == p.nchunks - 1 ? p.rows : out_r0 + p.chunk_rows;  // the last chunk takes the remainder
     const int in_r0 = out_r0 - K;
     const int in_r1 = out_r1 + K;            // exclusive
 
@@ -287,6 +337,7 @@ __device__ __forceinline__ void stream_band(const PassParams &p, Feed &feed, con
                 if ((K - 1) & 1) o[i] = __byte_perm(E[i], O[i], 0x7351);
                 else o[i] = __byte_perm(E[i] >> 4, O[i] >> 4, 0x6240);
             }
+            B2C_DBG_RANGE("local store", p.dbg_rank, dst, st_bytes, p.dbg_dst_lo, p.dbg_dst_hi);
             if (!GENERAL || st_bytes == SB) store_strip<NW>(dst, o);
             else store_strip_partial<NW>(dst, o, st_bytes);
 
@@ -311,17 +362,23 @@ __device__ __forceinline__ void stream_band(const PassParams &p, Feed &feed, con
                     const long long up = (long long)p.rows * p.pitch, dn = -up;
                     const bool rt = orow < F, rb = orow >= p.rows - F;
                     const bool cw = xs < F * CH, ce = xs + SB > p.bw - F * CH;
-                    if (top && rt && h.peer_dst[B2C_N]) store_strip<NW>(h.peer_dst[B2C_N] + doff + up, o);
-                    if (bot && rb && h.peer_dst[B2C_S]) store_strip<NW>(h.peer_dst[B2C_S] + doff + dn, o);
+                    auto put = [&](const int d, const long long off) {
+                        uint8_t *const q = h.peer_dst[d] + off;
+                        B2C_DBG_RANGE("peer store", p.dbg_rank, q, SB, h.peer_dst[d] - p.dbg_peer_before,
+                                      h.peer_dst[d] + p.dbg_peer_after);
+                        store_strip<NW>(q, o);
+                    };
+                    if (top && rt && h.peer_dst[B2C_N]) put(B2C_N, doff + up);
+                    if (bot && rb && h.peer_dst[B2C_S]) put(B2C_S, doff + dn);
                     if (west && cw) {
-                        if (h.peer_dst[B2C_W]) store_strip<NW>(h.peer_dst[B2C_W] + doff + p.bw, o);
-                        if (top && rt && h.peer_dst[B2C_NW]) store_strip<NW>(h.peer_dst[B2C_NW] + doff + up + p.bw, o);
-                        if (bot && rb && h.peer_dst[B2C_SW]) store_strip<NW>(h.peer_dst[B2C_SW] + doff + dn + p.bw, o);
+                        if (h.peer_dst[B2C_W]) put(B2C_W, doff + p.bw);
+                        if (top && rt && h.peer_dst[B2C_NW]) put(B2C_NW, doff + up + p.bw);
+                        if (bot && rb && h.peer_dst[B2C_SW]) put(B2C_SW, doff + dn + p.bw);
                     }
                     if (east && ce) {
-                        if (h.peer_dst[B2C_E]) store_strip<NW>(h.peer_dst[B2C_E] + doff - p.bw, o);
-                        if (top && rt && h.peer_dst[B2C_NE]) store_strip<NW>(h.peer_dst[B2C_NE] + doff + up - p.bw, o);
-                        if (bot && rb && h.peer_dst[B2C_SE]) store_strip<NW>(h.peer_dst[B2C_SE] + doff + dn - p.bw, o);
+                        if (h.peer_dst[B2C_E]) put(B2C_E, doff - p.bw);
+                        if (top && rt && h.peer_dst[B2C_NE]) put(B2C_NE, doff + up - p.bw);
+                        if (bot && rb && h.peer_dst[B2C_SE]) put(B2C_SE, doff + dn - p.bw);
                     }
                 }
             }
@@ -387,7 +444,10 @@ struct LdgFeed {
     __device__ __forceinline__ void start(int x0, int in_r0, int in_r1_) {
         in_r1 = in_r1_;
         src = p.src + (long long)in_r0 * p.pitch + x0 + lane * NW * 4;
-        // rows up to in_r1+4 are read without a guard: the frame has kFrameRows >= 8+4 rows
+        // rows up to in_r1+2 are read without a guard: the frame has kFrameRows >= F+K+4 rows
+        B2C_DBG_RANGE("feed first row", p.dbg_rank, src, NW * 4, p.dbg_src_lo, p.dbg_src_hi);
+        B2C_DBG_RANGE("feed last row", p.dbg_rank, src + (long long)((in_r1 - in_r0 + 2) / 3 * 3 - 1) * p.pitch, NW * 4,
+                      p.dbg_src_lo, p.dbg_src_hi);
         load_strip<NW>(src, na);
         load_strip<NW>(src + p.pitch, nb);
         load_strip<NW>(src + 2 * p.pitch, nc);
@@ -410,6 +470,65 @@ struct LdgFeed {
 };
 
 
+// Ring warps before they touch a halo frame: lanes 0-7 poll the data flag of direction `lane`,
+// lanes 8-15 the ack word of direction `lane - 8`, all at once.
+__device__ __forceinline__ void halo_wait(const HaloParams &h, const unsigned dmask, const uint32_t E, const int lane) {
+    const int d = lane & 7;
+    const bool ack = lane >= 8;
+    const bool want = lane < 16 && ((dmask >> d) & 1u) && h.peer_flag[d] != nullptr &&
+                      (h.mode & (ack ? kHaloWaitAck : kHaloWaitData));
+    if (want) {
+        if (h.delay > 0) { const long long t0 = clock64(); while (clock64() - t0 < h.delay) {} }
+        const uint32_t *const f = (ack ? h.acks : h.flags) + d * 32;
+        const long long t0 = clock64();
+        uint32_t have;
+        while ((int)((have = ld_relaxed_sys(f)) - E) < 0) {
+            if (clock64() - t0 > (20ll << 30)) {  // ~10 s: a peer died or the protocol broke
+                printf("b200conv: halo %s wait timeout dir=%d want=%u have=%u\n", ack ? "ack" : "data", d, E, have);
+                __trap();
+            }
+        }
+#ifdef B2C_DEBUG
+        if ((int)(have - E) > 1) {   // a neighbour can be at most one exchange ahead
+            printf("b200conv DEBUG: %s epoch dir=%d ran ahead: want=%u have=%u\n", ack ? "ack" : "data", d, E, have);
+            __trap();
+        }
+#endif
+        (void)ld_acquire_sys(f);   // orders the frame reads / remote stores below after the flag
+        if (h.prof) {
+            const unsigned long long dt = (unsigned long long)(clock64() - t0);
+            atomicAdd(h.prof + (ack ? 8 : 0) + d, dt);
+            atomicMax(h.prof + 24 + (ack ? 8 : 0) + d, dt);
+            atomicAdd(h.prof + 16, 1ull);
+        }
+    }
+    __syncwarp();
+}
+
+// Ring warps after their band: every lane's remote stores are issued; lanes 0-7 each take one
+// direction, make the warp's stores visible system-wide, count in, and the last arriver of a
+// direction publishes the epoch (data: E+1 into the neighbour's flag; ack: E into its ack word).
+__device__ __forceinline__ void halo_publish(const HaloParams &h, const unsigned dmask, const uint32_t E,
+                                             const int lane, const bool data) {
+    __syncwarp();
+    const bool mine = lane < 8 && ((dmask >> lane) & 1u) && h.peer_flag[lane] != nullptr;
+    if (mine) {
+        const long long t0 = h.prof ? clock64() : 0;
+        __threadfence_system();   // one fence per warp instruction; the barrier above makes it cover all lanes
+        const unsigned old = atomicAdd(h.counters + lane * 32, 1u);
+        if ((int)old + 1 == h.expected[lane]) {
+            h.counters[lane * 32] = 0;
+            __threadfence_system();
+            if (data) st_release_sys(h.peer_flag[lane], E + 1u);
+            else st_release_sys(h.peer_ack[lane], E);
+        }
+        if (h.prof) {
+            atomicAdd(h.prof + 17, (unsigned long long)(clock64() - t0));
+            atomicAdd(h.prof + 18, 1ull);
+        }
+    }
+}
+
 // Whole per-warp program shared by the LDG and TMA kernels: pick the work item, wait for the
 // neighbours' epoch if this warp touches a halo frame, stream the band, publish our epoch.
 template <int K, int NW, int CH, bool CHECK, class MakeFeed>
@@ -420,7 +539,7 @@ __device__ __forceinline__ void stream_warp(const PassParams &p, const int wid, 
     constexpr int SB = NW * 4;
     const int x0 = band * p.vw - p.hlo;
     const int in_r0 = chunk * p.chunk_rows - K;
-    const int in_r1 = min((chunk + 1) * p.chunk_rows, p.rows) + K;
+    const int in_r1 = (chunk == p.nchunks - 1 ? p.rows : (chunk + 1) * p.chunk_rows) + K;
     const bool edge = (p.zero_w && x0 < 0) || (p.zero_e && x0 + 32 * SB > p.bw) ||
                       (p.zero_n && in_r0 < 0) || (p.zero_s && in_r1 > p.rows);
     const bool partial = (p.bw % SB) != 0 && (band + 1) * p.vw >= p.bw;  // owns the cut last strip
@@ -434,32 +553,21 @@ __device__ __forceinline__ void stream_warp(const PassParams &p, const int wid, 
     if (p.converged && *p.converged) return;  // fixed point already reached: nothing changes any more
 
     bool top = false, bot = false, west = false, east = false;
+    unsigned dmask = 0;   // directions whose ring this warp belongs to (bit = B2C_N .. B2C_SE)
+    uint32_t E = 0;
     const HaloParams &h = p.halo;
     if (h.enabled) {
         // ring membership, by the same formulas the host used for h.expected[]
         top = chunk == 0; bot = chunk == p.nchunks - 1;
         west = band < h.nbw; east = band >= p.nbands - h.nbe;
-        const bool dirs[8] = {top, bot, west, east, top && west, top && east, bot && west, bot && east};
-        if (top || bot || west || east) {
-            if (lane == 0) {
-                if (h.delay > 0) { const long long t0 = clock64(); while (clock64() - t0 < h.delay) {} }
-#pragma unroll
-                for (int d = 0; d < 8; ++d) {
-                    if (!dirs[d] || !h.peer_flag[d]) continue;
-                    const long long t0 = clock64();
-                    while ((int)(ld_acquire_sys(h.flags + d * 32) - h.wait_epoch) < 0) {
-                        if (clock64() - t0 > (20ll << 30)) {  // ~10 s: a peer died or the protocol broke
-                            printf("b200conv: halo wait timeout dir=%d want=%u have=%u\n", d, h.wait_epoch,
-                                   ld_acquire_sys(h.flags + d * 32));
-                            __trap();
-                        }
-                    }
-                }
-            }
-            __syncwarp();
+        dmask = (top ? 1u : 0u) | (bot ? 2u : 0u) | (west ? 4u : 0u) | (east ? 8u : 0u) | (top && west ? 16u : 0u) |
+                (top && east ? 32u : 0u) | (bot && west ? 64u : 0u) | (bot && east ? 128u : 0u);
+        if (dmask) {
+            E = h.epoch + (h.epoch_base ? __ldcg(h.epoch_base) : 0u);
+            if (h.mode & (kHaloWaitData | kHaloWaitAck)) halo_wait(h, dmask, E, lane);
         }
     }
-    const bool do_push = h.enabled && h.push && (top || bot || west || east);
+    const bool do_push = dmask != 0 && (h.mode & kHaloPush) && h.fused;
 
     auto feed = make_feed();
     if (edge || partial || do_push)
@@ -467,25 +575,7 @@ __device__ __forceinline__ void stream_warp(const PassParams &p, const int wid, 
     else
         stream_band<K, NW, CH, false, CHECK>(p, feed, band, chunk, lane, false, false, false, false, false);
 
-    if (do_push) {
-        // All of this warp's remote stores are issued; make them visible system-wide,
-        // then count in.  The last pusher per direction publishes the epoch.
-        __threadfence_system();
-        __syncwarp();
-        if (lane == 0) {
-            const bool dirs[8] = {top, bot, west, east, top && west, top && east, bot && west, bot && east};
-#pragma unroll
-            for (int d = 0; d < 8; ++d) {
-                if (!dirs[d] || !h.peer_flag[d]) continue;
-                const unsigned old = atomicAdd(h.counters + d * 32, 1u);
-                if ((int)old + 1 == h.expected[d]) {
-                    h.counters[d * 32] = 0;
-                    __threadfence_system();
-                    st_release_sys(h.peer_flag[d], h.post_epoch);
-                }
-            }
-        }
-    }
+    if (dmask != 0 && (do_push || (h.mode & kHaloPostAck))) halo_publish(h, dmask, E, lane, do_push);
 }
 
 template <int K, int NW, int CH, bool CHECK>

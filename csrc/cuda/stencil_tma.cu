@@ -14,6 +14,8 @@
 #include <cuda.h>
 #include <cuda_runtime.h>
 
+#include <mutex>
+
 #include "common.h"
 #include "kernels.h"
 #include "stencil_stream.cuh"
@@ -62,11 +64,13 @@ struct TmaFeed {
     const int lane;
     const uint32_t ring, bars;
     const int depth;
+    const int org_x, org_y;         // allocation coordinates of the pass origin (PassParams::org_x/org_y)
     int cx, cy, ngroups, g;
     uint32_t a[NW], b[NW], c[NW];   // the three rows of the current group
 
-    __device__ __forceinline__ TmaFeed(const CUtensorMap *tm_, int lane_, uint32_t ring_, uint32_t bars_, int depth_)
-        : tm(tm_), lane(lane_), ring(ring_), bars(bars_), depth(depth_) {}
+    __device__ __forceinline__ TmaFeed(const CUtensorMap *tm_, int lane_, uint32_t ring_, uint32_t bars_, int depth_,
+                                       int org_x_, int org_y_)
+        : tm(tm_), lane(lane_), ring(ring_), bars(bars_), depth(depth_), org_x(org_x_), org_y(org_y_) {}
 
     __device__ __forceinline__ void issue(int grp) {  // one lane
         const int slot = grp % depth;
@@ -78,13 +82,16 @@ struct TmaFeed {
 
     __device__ __forceinline__ void start(int x0, int in_r0, int in_r1) {
         ngroups = (in_r1 - in_r0 + kTmaRows - 1) / kTmaRows;
-        cx = kLeftPad + x0;        // tensor coordinates are relative to the allocation
-        cy = kFrameRows + in_r0;
+        cx = org_x + x0;           // tensor coordinates are relative to the allocation
+        cy = org_y + in_r0;
         g = 0;
         if (lane == 0) {
             for (int i = 0; i < depth; ++i) mbar_init(bars + 8u * i, 1);
             asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            // Halo frames are written by peers (and by the previous pass) with ordinary stores; the
+            // tiles below are read through the async proxy.  After the flag acquire in stream_warp a
+            // cross-proxy fence is needed before the first bulk copy may read those bytes.
+            asm volatile("fence.proxy.async;" ::: "memory");
             const int n = ngroups < depth ? ngroups : depth;
             for (int i = 0; i < n; ++i) issue(i);
         }
@@ -134,7 +141,7 @@ stream_tma_kernel(const __grid_constant__ CUtensorMap tm, const PassParams p, co
     constexpr int kStage = TmaFeed<NW>::kStage;
     const uint32_t ring = smem_u32(smem) + (uint32_t)(warp * depth) * kStage;
     const uint32_t bars = smem_u32(smem) + (uint32_t)(kWarpsPerCta * depth) * kStage + (uint32_t)(warp * depth) * 8u;
-    stream_warp<K, NW, CH, CHECK>(p, wid, lane, [&]() { return TmaFeed<NW>(&tm, lane, ring, bars, depth); });
+    stream_warp<K, NW, CH, CHECK>(p, wid, lane, [&]() { return TmaFeed<NW>(&tm, lane, ring, bars, depth, p.org_x, p.org_y); });
 }
 
 // ------------------------------------------------------------------ host side
@@ -193,11 +200,15 @@ static cudaError_t tma_op_t(int op, TmaState *t, const PassParams *p, int src_in
                             int *occ_out) {
     auto fn = check ? stream_tma_kernel<K, NW, CH, true> : stream_tma_kernel<K, NW, CH, false>;
     constexpr int kStage = TmaFeed<NW>::kStage;
-    static int depth = 0;
-    static bool cfg_done[64][2];  // cudaFuncSetAttribute is per device
+    // ring depth and the shared-memory opt-in are per (device, variant)
+    static int depth_tab[64][2];
+    static bool cfg_done[64][2];
+    static std::mutex mu;
+    std::lock_guard<std::mutex> lock(mu);
     int dev = 0;
     cudaGetDevice(&dev);
     bool &cfg = cfg_done[dev & 63][check ? 1 : 0];
+    int &depth = depth_tab[dev & 63][check ? 1 : 0];
     if (!depth) {
         int by_regs = 0;
         cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&by_regs, fn, kWarpsPerCta * 32, 0);

@@ -42,6 +42,8 @@ struct Shared {
     double phase_ms[kMaxWorkers][5];  // read, upload, loop, download, write
     int iterations[kMaxWorkers];
     char plan[kMaxWorkers][512];
+    double tune_ms[kMaxWorkers][16];      // coupled tuning: every rank's time per candidate
+    long long start_wait[kMaxWorkers];    // SM cycles each rank spent in the device-side start barrier
 };
 
 double now_ms() {
@@ -133,20 +135,47 @@ int worker(const b2c_cli &cli, int rank, int n, int P, int Q, Shared *sh) {
     double t = now_ms();
     WB2C(b2c_read_block(cli.image, host, row_bytes, W, H, CH, row0, col0, R, C));   // :126-140
     sh->phase_ms[rank][0] = now_ms() - t;
-    t = now_ms();
-    WB2C(b2c_engine_upload(e, host, 0, s));
-    WCK(cudaStreamSynchronize(s));
-    sh->phase_ms[rank][1] = now_ms() - t;
 
     if (n > 1) {
         WB2C(b2c_engine_export(e, sh->blobs[rank]));
         if (!barrier(sh, n)) return 1;
         WB2C(b2c_engine_import(e, sh->blobs, n));
-        if (!barrier(sh, n)) return 1;  // every block uploaded, every peer mapped
+        if (!barrier(sh, n)) return 1;  // every peer mapped
+        // rows per warp: a few candidates timed with the halo exchange live, all ranks together;
+        // the slowest rank's time decides (the buffers hold no image yet)
+        const int nc = b2c_engine_tune_count(e);
+        if (nc > 0) {
+            for (int i = 0; i < nc && i < 16; ++i) {
+                const double ms = b2c_engine_tune_time(e, i, s);
+                if (ms < 0) {
+                    fprintf(stderr, "b200conv[%d]: %s\n", rank, b2c_last_error());
+                    return 1;
+                }
+                sh->tune_ms[rank][i] = ms;
+            }
+            if (!barrier(sh, n)) return 1;
+            int best = 0;
+            double best_ms = 1e300;
+            for (int i = 0; i < nc && i < 16; ++i) {
+                double worst = 0;
+                for (int k = 0; k < n; ++k) worst = sh->tune_ms[k][i] > worst ? sh->tune_ms[k][i] : worst;
+                if (worst < best_ms) { best_ms = worst; best = i; }
+            }
+            WB2C(b2c_engine_tune_set(e, best));
+            if (!barrier(sh, n)) return 1;
+        }
     }
+    t = now_ms();
+    WB2C(b2c_engine_upload(e, host, 0, s));
+    WCK(cudaStreamSynchronize(s));
+    sh->phase_ms[rank][1] = now_ms() - t;
+    if (n > 1 && !barrier(sh, n)) return 1;  // every block uploaded before a frame is written
     WB2C(b2c_engine_exchange(e, s));
     WCK(cudaStreamSynchronize(s));
-    if (n > 1 && !barrier(sh, n)) return 1;  // MPI_Barrier before the timer, :151-154
+    if (n > 1) {
+        if (!barrier(sh, n)) return 1;       // MPI_Barrier before the timer, :151-154 ...
+        WB2C(b2c_engine_barrier(e, s));      // ... finished on the device: the streams start within microseconds
+    }
 
     char out_name[4096];
     b2c_output_name(cli.image, out_name, sizeof out_name);
@@ -185,6 +214,7 @@ int worker(const b2c_cli &cli, int rank, int n, int P, int Q, Shared *sh) {
     sh->phase_ms[rank][3] = dl_ms;
     sh->phase_ms[rank][4] = wr_ms;
     sh->iterations[rank] = executed;
+    sh->start_wait[rank] = n > 1 ? (long long)b2c_engine_barrier_wait_cycles(e) : 0;
     b2c_engine_describe(e, sh->plan[rank], sizeof sh->plan[rank]);
     if (n > 1) {
         // cudaIpc tear-down order: all writes done -> everyone unmaps -> everyone frees
@@ -236,6 +266,8 @@ void write_json(const b2c_cli &cli, int n, int P, int Q, const Shared *sh, doubl
             n > 1 ? 2 * C * cli.channels + 2 * R * cli.channels + 4 * cli.channels : 0,
             gpix > 0 ? 100.0 * gpix / (6555.5 / 2 / cli.channels * n) : 0.0, json_escape(sh->plan[0]).c_str());
     for (int k = 0; k < n; ++k) fprintf(f, "%s%.4f", k ? ", " : "", sh->loop_ms[k]);
+    fprintf(f, "], \"start_barrier_wait_cycles\": [");
+    for (int k = 0; k < n; ++k) fprintf(f, "%s%lld", k ? ", " : "", sh->start_wait[k]);
     fprintf(f, "]}\n");
     fclose(f);
 }

@@ -159,6 +159,7 @@ typedef struct b2c_emul_opts {
     int stall_ms;        /*   convergence slots; -1 / 0 = nobody                            */
     int images;          /* > 1: that many images back to back through the same buffers with no */
                          /*   barrier in between (image j = input XOR 37*j); needs check_every 0 */
+    int halo_depth;      /* iterations between two halo exchanges (multiple of tb, <= 32); 0 = tb  */
 } b2c_emul_opts;
 
 /* Returns B2C_OK (out = the gathered result of every image, max(1, images) x H x W*CH bytes;
@@ -197,6 +198,8 @@ typedef struct b2c_opts {
     int use_graph;    /* capture the pass loop in a CUDA graph: -1 auto, 0, 1 */
     int check_every;  /* fused convergence check period in iterations, 0 = off (ignored by the
                          naive kernel and cuda-compat, which have no change detector) */
+    int halo_depth;   /* multi-rank: iterations between two halo exchanges = depth of the halo a
+                         rank keeps (a multiple of tb, at most 32); 0 = auto */
 } b2c_opts;
 
 void b2c_default_opts(b2c_opts *o);
@@ -244,6 +247,34 @@ int b2c_engine_exchange(b2c_engine *e, void *stream);
  * from inside the stencil kernel (replaces mpi_convolution.c:156-240). */
 int b2c_engine_run(b2c_engine *e, int repetitions, void *stream);
 
+/* b2c_engine_run cut into its passes, for callers that interleave several engines on ONE device
+ * (tests/parallel/local.py): plan_run returns the number of passes of a `repetitions` run,
+ * run_pass enqueues pass i.  Every rank must have enqueued pass i before any rank enqueues i+1. */
+int b2c_engine_plan_run(b2c_engine *e, int repetitions);
+int b2c_engine_run_pass(b2c_engine *e, int i, void *stream);
+
+/* Coupled tuning of the rows-per-warp of a multi-rank engine (collective: every rank makes the
+ * same calls in the same order, after the peers are connected and before data is loaded).
+ * tune_count: number of candidates (0: nothing to tune); tune_time: milliseconds of a short
+ * coupled run with candidate i on this rank (reduce with MAX over ranks); tune_set: adopt
+ * candidate i (-1 = the modelled plan).  No counterpart in the reference. */
+int b2c_engine_tune_count(const b2c_engine *e);
+double b2c_engine_tune_time(b2c_engine *e, int i, void *stream);
+int b2c_engine_tune_set(b2c_engine *e, int i);
+
+/* Device-side barrier over peer memory (replaces MPI_Barrier in front of the timer,
+ * mpi_convolution.c:151): work enqueued on `stream` after it starts within microseconds on all
+ * ranks.  Collective.  barrier_wait_cycles: SM clocks this rank spent in the last one (synchronises). */
+int b2c_engine_barrier(b2c_engine *e, void *stream);
+int64_t b2c_engine_barrier_wait_cycles(b2c_engine *e);
+
+/* Opt-in wait-time counters of the halo protocol (also B200CONV_HALO_PROF=1): 40 words,
+ * [0..7] cycles ring warps waited for the data epoch per direction, [8..15] same for the ack
+ * epoch, [16] number of waits, [17] cycles spent in fence + count-in + publish, [18] number of
+ * those, [24..31] / [32..39] longest single data / ack wait per direction. */
+int b2c_engine_set_profile(b2c_engine *e, int on);
+int b2c_engine_halo_profile(b2c_engine *e, uint64_t out[40], int reset);
+
 /* Iterations actually executed by the last run (differs from `repetitions`
  * only with CUDA_COMPAT odd counts or a convergence early-exit).  Synchronises. */
 int b2c_engine_iterations_done(b2c_engine *e);
@@ -282,7 +313,7 @@ int b2c_blur_device(const uint8_t *d_in, int64_t in_pitch, uint8_t *d_out, int64
  * The call performs no cudaMalloc/cudaFree and no allocating library call.  Its two work
  * buffers and flag words live in a fixed 32 MiB scratch array that is part of the library
  * image (every GPU that loads the library holds it until the process exits).  Limit: the
- * padded image must fit, 2 * (round_up(W*CH + 80, 128) * (H + 24) + 1024) + 4096 <= 32 MiB,
+ * padded image must fit, 2 * (round_up(W*CH + 256, 128) * (H + 80) + 1024) + 8192 <= 32 MiB,
  * which covers images up to about 1920x2520 rgb; larger ones are rejected with
  * B2C_ETOOBIG and a message from b2c_last_error().
  *
@@ -311,6 +342,12 @@ int b2c_debug_map_work(int id, int nbands, int nchunks, int nbw, int nbe, int *b
  * out = {hlo, vw, nbands, nchunks, chunk_rows, nbw, nbe, K, strip_bytes, halo_depth}. */
 int b2c_debug_band_plan(int rows, int cols, int channels, int has_neighbours, int tb, int strip_bytes,
                         int chunk_rows, int kernel, int sm_count, int out[10]);
+
+/* Test hook (host only): the passes of a `reps`-iteration run of a rank with eight neighbours and
+ * the plan of each; 12 ints per pass {k, ext, mode, group_end, rows, row_bytes, nbands, nchunks,
+ * chunk_rows, last_chunk_rows, nbw, nbe}.  Returns the number of passes. */
+int b2c_debug_pass_plans(int rows, int cols, int channels, int has_neighbours, int tb, int strip_bytes,
+                         int chunk_rows, int halo_depth, int reps, int sm_count, int *out, int max_passes);
 
 /* Whole-program equivalent of cuda/main.c:10-53 (read file, blur, write
  * blur_<name>) on one GPU; returns loop milliseconds in *loop_ms. */

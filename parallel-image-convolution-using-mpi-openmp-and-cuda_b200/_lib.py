@@ -30,12 +30,14 @@ DIRS = ("N", "S", "W", "E", "NW", "NE", "SW", "SE")
 
 class Opts(C.Structure):
     _fields_ = [(n, C.c_int) for n in
-                ("boundary", "filter", "kernel", "tb", "strip_bytes", "chunk_rows", "use_graph", "check_every")]
+                ("boundary", "filter", "kernel", "tb", "strip_bytes", "chunk_rows", "use_graph", "check_every",
+                 "halo_depth")]
 
 
 class EmulOpts(C.Structure):
     _fields_ = [("tb", C.c_int), ("check_every", C.c_int), ("max_delay_us", C.c_int), ("seed", C.c_uint),
-                ("timeout_ms", C.c_int), ("single_slot_set", C.c_int), ("stall_rank", C.c_int), ("stall_ms", C.c_int), ("images", C.c_int)]
+                ("timeout_ms", C.c_int), ("single_slot_set", C.c_int), ("stall_rank", C.c_int), ("stall_ms", C.c_int), ("images", C.c_int),
+                ("halo_depth", C.c_int)]
 
 
 class Cli(C.Structure):
@@ -93,6 +95,16 @@ def _load() -> C.CDLL:
         "b2c_engine_exchange": (I, [P, V]),
         "b2c_engine_run": (I, [P, I, V]),
         "b2c_engine_iterations_done": (I, [P]),
+        "b2c_engine_plan_run": (I, [P, I]),
+        "b2c_engine_run_pass": (I, [P, I, V]),
+        "b2c_engine_tune_count": (I, [P]),
+        "b2c_engine_tune_time": (C.c_double, [P, I, V]),
+        "b2c_engine_tune_set": (I, [P, I]),
+        "b2c_engine_barrier": (I, [P, V]),
+        "b2c_engine_barrier_wait_cycles": (L, [P]),
+        "b2c_engine_set_profile": (I, [P, I]),
+        "b2c_engine_halo_profile": (I, [P, C.POINTER(C.c_uint64 * 40), I]),
+        "b2c_debug_pass_plans": (I, [I, I, I, I, I, I, I, I, I, I, C.POINTER(I), I]),
         "b2c_engine_launches": (L, [P]),
         "b2c_resident_plan": (I, [I, I, I, I, I, C.POINTER(I)]),
         "b2c_debug_map_work": (I, [I, I, I, I, I, C.POINTER(I), C.POINTER(I)]),
@@ -125,12 +137,12 @@ def check(rc: int, what: str = "b200conv") -> int:
 
 
 def make_opts(boundary="zero", filter="gaussian", kernel="auto", tb=0, strip_bytes=0, chunk_rows=0,
-              use_graph=-1, check_every=0) -> Opts:
+              use_graph=-1, check_every=0, halo_depth=0) -> Opts:
     o = Opts()
     lib.b2c_default_opts(C.byref(o))
     o.boundary = BOUNDARY[boundary] if isinstance(boundary, str) else int(boundary)
     o.filter = FILTER[filter] if isinstance(filter, str) else int(filter)
     o.kernel = KERNEL[kernel] if isinstance(kernel, str) else int(kernel)
     o.tb, o.strip_bytes, o.chunk_rows = int(tb), int(strip_bytes), int(chunk_rows)
-    o.use_graph, o.check_every = int(use_graph), int(check_every)
+    o.use_graph, o.check_every, o.halo_depth = int(use_graph), int(check_every), int(halo_depth)
     return o

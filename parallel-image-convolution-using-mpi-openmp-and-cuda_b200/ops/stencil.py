@@ -132,6 +132,47 @@ class Engine:
     def iterations_done(self) -> int:
         return check(lib.b2c_engine_iterations_done(self._h), "engine_iterations_done")
 
+    def plan_run(self, repetitions: int) -> int:
+        """Number of passes of a ``repetitions`` run; enqueue them one by one with :meth:`run_pass`."""
+        return check(lib.b2c_engine_plan_run(self._h, int(repetitions)), "engine_plan_run")
+
+    def run_pass(self, i: int, stream=None):
+        check(lib.b2c_engine_run_pass(self._h, int(i), _stream_ptr(stream)), "engine_run_pass")
+
+    # -- coupled tuning, device barrier, protocol counters (multi-rank) --------
+    def tune_count(self) -> int:
+        return check(lib.b2c_engine_tune_count(self._h), "engine_tune_count")
+
+    def tune_time(self, i: int, stream=None) -> float:
+        ms = float(lib.b2c_engine_tune_time(self._h, int(i), _stream_ptr(stream)))
+        if ms < 0:
+            raise B2CError(f"engine_tune_time: {last_error()}")
+        return ms
+
+    def tune_set(self, i: int):
+        check(lib.b2c_engine_tune_set(self._h, int(i)), "engine_tune_set")
+
+    def barrier(self, stream=None):
+        """Device-side barrier over peer memory (collective)."""
+        check(lib.b2c_engine_barrier(self._h, _stream_ptr(stream)), "engine_barrier")
+
+    def barrier_wait_cycles(self) -> int:
+        return check(lib.b2c_engine_barrier_wait_cycles(self._h), "engine_barrier_wait_cycles")
+
+    def set_profile(self, on: bool = True):
+        check(lib.b2c_engine_set_profile(self._h, int(bool(on))), "engine_set_profile")
+
+    def halo_profile(self, reset: bool = True) -> dict:
+        """Wait-time counters of the halo protocol (SM cycles, summed over ring warps)."""
+        from .._lib import DIRS
+
+        buf = (C.c_uint64 * 40)()
+        check(lib.b2c_engine_halo_profile(self._h, C.byref(buf), int(bool(reset))), "engine_halo_profile")
+        v = list(buf)
+        return {"data_wait_cycles": dict(zip(DIRS, v[0:8])), "ack_wait_cycles": dict(zip(DIRS, v[8:16])),
+                "waits": v[16], "publish_cycles": v[17], "publishes": v[18],
+                "data_wait_max": dict(zip(DIRS, v[24:32])), "ack_wait_max": dict(zip(DIRS, v[32:40]))}
+
 
 _CACHE: "OrderedDict[tuple, Engine]" = OrderedDict()
 _CACHE_MAX = 4

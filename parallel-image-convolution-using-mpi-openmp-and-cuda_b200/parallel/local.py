@@ -63,19 +63,22 @@ class LocalGrid:
                 with torch.cuda.device(self.devices[k]):
                     e.run(repetitions)
             return
-        left = int(repetitions)
-        step = max(1, self.tb)
         if int(self.engines[0].opts.check_every) and len(self.engines) > 1:
             # the cross-rank OR waits on every rank's kernel: impossible to emulate on one GPU
             raise ValueError("check_every needs one GPU per rank")
-        while left > 0:
-            k = step
-            while k > left:  # exactly ONE pass per rank per round: k in {tb, tb/2, ..., 1}
-                k //= 2
+        if int(self.engines[0].opts.check_every) or self.engines[0].describe().startswith("kernel=resident"):
             for r, e in enumerate(self.engines):
                 with torch.cuda.device(self.devices[r]):
-                    e.run(k)
-            left -= k
+                    e.run(repetitions)
+            return
+        # exactly ONE pass per rank per round, in the engines' own pass order (groups of passes
+        # between two halo exchanges included): every flag a kernel waits for is set before it starts
+        counts = [e.plan_run(repetitions) for e in self.engines]
+        assert len(set(counts)) == 1, counts
+        for i in range(counts[0]):
+            for r, e in enumerate(self.engines):
+                with torch.cuda.device(self.devices[r]):
+                    e.run_pass(i)
 
     def gather(self) -> torch.Tensor:
         shape = (self.height, self.width) if self.channels == 1 else (self.height, self.width, self.channels)

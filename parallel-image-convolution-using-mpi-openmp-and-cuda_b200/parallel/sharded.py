@@ -19,6 +19,7 @@ from .decomposition import decompose
 
 class ShardedBlur:
     def __init__(self, width, height, channels, group=None, grid=None, device=None, **opts):
+        self.tuned = None
         if not dist.is_initialized():
             raise RuntimeError("torch.distributed is not initialised")
         self.group = group
@@ -36,8 +37,25 @@ class ShardedBlur:
             allh = [torch.empty(HANDLE_BYTES, dtype=torch.uint8, device=mine.device) for _ in range(self.world)]
             dist.all_gather(allh, mine, group=group)
             self.engine.import_handles([bytes(t.cpu().numpy().tobytes()) for t in allh])
+            self.tuned = self._tune_coupled()
         self._ev0 = torch.cuda.Event(enable_timing=True)
         self._ev1 = torch.cuda.Event(enable_timing=True)
+
+    def _tune_coupled(self):
+        """Rows per warp are chosen by timing a few candidates with the halo exchange live, all
+        ranks together (the optimum without neighbours is wrong once ring warps gate them)."""
+        n = self.engine.tune_count()
+        if n <= 0:
+            return None
+        dist.barrier(group=self.group)   # every rank has imported: nobody writes into an unmapped peer
+        ms = torch.tensor([self.engine.tune_time(i) for i in range(n)], dtype=torch.float64,
+                          device=f"cuda:{self.device}")
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX, group=self.group)
+        best = int(torch.argmin(ms).item())
+        self.engine.tune_set(best)
+        torch.cuda.synchronize(self.device)
+        dist.barrier(group=self.group)
+        return {"candidate": best, "ms": [round(float(x), 4) for x in ms.tolist()]}
 
     # geometry of this rank's block
     @property
@@ -88,6 +106,7 @@ class ShardedBlur:
         torch.cuda.synchronize(self.device)
         if self.world > 1:
             dist.barrier(group=self.group)
+            self.engine.barrier()   # device-side: the timed region starts within microseconds on all ranks
         self._ev0.record()
         self.engine.run(repetitions)
         self._ev1.record()

@@ -53,6 +53,29 @@ def test_images_back_to_back_without_a_barrier(grid, boundary, reps):
         assert (out == reference_oracle(img ^ np.uint8((37 * j) & 255), reps, boundary)).all(), j
 
 
+@pytest.mark.parametrize("grid,boundary", [((2, 2), "zero"), ((2, 4), "torus"), ((1, 2), "torus"), ((3, 3), "zero"),
+                                           ((1, 1), "torus")])
+@pytest.mark.parametrize("tb,halo_depth,reps", [(4, 8, 21), (4, 12, 30), (4, 16, 37), (2, 6, 13), (1, 3, 7), (8, 16, 40)])
+def test_one_exchange_per_group_of_passes(grid, boundary, tb, halo_depth, reps):
+    # a rank keeps a halo `halo_depth` deep and exchanges it once per `halo_depth` iterations; the
+    # passes in between recompute the shrinking halo themselves and write the frames of both
+    # buffers, which is what the ack epoch protects (skewed ranks, odd remainders, short last group)
+    img = rnd(48, 48, 3, seed=12)
+    out, iters = threaded_halo_model(img, reps, grid, boundary, tb=tb, halo_depth=halo_depth, max_delay_us=200, seed=reps)
+    assert iters == reps
+    assert (out == reference_oracle(img, reps, boundary)).all(), (grid, boundary, tb, halo_depth, reps)
+
+
+def test_grouped_exchange_with_images_back_to_back_and_with_checks():
+    img = rnd(32, 64, 1, seed=13)
+    outs, _ = threaded_halo_model(img, 19, (2, 4), "torus", tb=4, halo_depth=8, max_delay_us=300, seed=2, images=4)
+    for j, out in enumerate(outs):
+        assert (out == reference_oracle(img ^ np.uint8((37 * j) & 255), 19, "torus")).all(), j
+    want = reference_oracle(img, 2000, "zero")
+    out, iters = threaded_halo_model(img, 2000, (2, 2), "zero", tb=4, halo_depth=16, check_every=12, max_delay_us=100, seed=4)
+    assert iters < 2000 and iters % 12 == 0 and (out == want).all()
+
+
 def test_halo_depth_is_clamped_to_the_block():
     img = rnd(4, 8, 1, seed=3)                      # 2x2 blocks on a 2x4 grid: tb=8 must clamp to 2
     out, _ = threaded_halo_model(img, 9, (2, 4), "torus", tb=8)
@@ -131,6 +154,24 @@ int main() {
             rc = b2c_emulate_halo_threads(in.data(), got.data(), W, H, ch, 400, boundary, 2, 2, &o, &iters);
             b2c_oracle_blur(in.data(), want.data(), W, H, ch, iters, boundary, B2C_GAUSSIAN);
             bad += rc != B2C_OK || memcmp(want.data(), got.data(), got.size()) != 0;
+        }
+    for (int boundary = 0; boundary <= 1; ++boundary)      // one exchange per group of passes: data + ack epochs
+        for (int hd = 8; hd <= 16; hd += 4) {
+            const int W2 = 64, H2 = 32, ch = 3, reps2 = 45;
+            std::vector<uint8_t> in((size_t)W2 * H2 * ch), want(in.size()), many(in.size() * 3), x(in.size());
+            srand(11);
+            for (auto &b : in) b = (uint8_t)rand();
+            b2c_emul_opts o;
+            memset(&o, 0, sizeof o);
+            o.tb = 4, o.max_delay_us = 50, o.seed = 5, o.stall_rank = -1, o.halo_depth = hd, o.images = 3;
+            int iters = 0;
+            int rc = b2c_emulate_halo_threads(in.data(), many.data(), W2, H2, ch, reps2, boundary, 2, 4, &o, &iters);
+            bad += rc != B2C_OK;
+            for (int j = 0; j < 3; ++j) {
+                for (size_t i = 0; i < in.size(); ++i) x[i] = (uint8_t)(in[i] ^ (uint8_t)(37 * j));
+                b2c_oracle_blur(x.data(), want.data(), W2, H2, ch, reps2, boundary, B2C_GAUSSIAN);
+                bad += memcmp(want.data(), many.data() + (size_t)j * in.size(), in.size()) != 0;
+            }
         }
     for (int boundary = 0; boundary <= 1; ++boundary) {   // CTA protocol of the resident kernel, 3 x 3 tiles
         const int RW_ = 488, RH_ = 130, reps2 = 13;

@@ -61,15 +61,64 @@ def test_plan_invariants_the_kernels_rely_on(rows, cols, ch, nb, tb, strip, chun
     assert K in (1, 2, 4, 8) and SB in (4, 8, 16) and K * (SB // 4) <= 16        # register budget
     if nb:
         assert K <= min(rows, cols) or K == 1                                   # a K-deep halo comes from one neighbour
-        assert F == K
+        assert F % K == 0 and K <= F <= 32 and (F <= min(rows, cols) or F == K)
     # window of a band: [band*vw - hlo, +32*SB); it must hold K*CH bytes of overlap on both sides
     assert vw > 0 and hlo % align == 0 and vw % align == 0
-    assert K * ch <= hlo <= 32                                                  # left frame is 32 bytes
+    assert K * ch <= hlo <= 32
     assert 32 * SB - hlo - vw >= K * ch
-    assert nbands == -(-bw // vw) and nchunks == -(-rows // chunk_rows) and 1 <= chunk_rows <= rows
+    assert nbands == -(-bw // vw) and 1 <= chunk_rows <= rows
+    last = rows - (nchunks - 1) * chunk_rows          # the last chunk takes the remainder
+    assert nchunks >= 1 and 1 <= last < 2 * chunk_rows + 64
     if nb:
-        # the whole F-deep ring must sit in the chunks / bands that push it
-        assert chunk_rows >= min(F, rows)
+        # the whole F-deep ring must sit in the chunks / bands that push it, and the chunks next to
+        # the first / last one must not reach into a frame (they do not wait for the flags)
+        assert chunk_rows >= min(max(F, 2 * K), rows)
+        assert nchunks == 1 or last >= max(F, 2 * K)
         assert nbw == nbands or nbw * vw >= F * ch
         assert nbe == nbands or (nbands - nbe) * vw <= bw - F * ch
         assert 1 <= nbw <= nbands and 1 <= nbe <= nbands
+    else:
+        assert nchunks == -(-rows // chunk_rows)
+
+
+@settings(max_examples=300, deadline=None)
+@given(rows=st.integers(8, 3000), cols=st.integers(8, 3000), ch=st.sampled_from([1, 3]),
+       tb=st.sampled_from([0, 1, 2, 4, 8]), strip=st.sampled_from([0, 4, 8, 16]), chunk=st.sampled_from([0, 1, 9, 64]),
+       halo_depth=st.sampled_from([0, 4, 8, 12, 16, 32]), reps=st.integers(1, 90))
+def test_pass_groups_of_a_rank_with_neighbours(rows, cols, ch, tb, strip, chunk, halo_depth, reps):
+    """One halo exchange per group of passes: what every pass of a group must satisfy so that the
+    kernels' ring-membership rules (first/last chunk, first/last bands) cover every frame access."""
+    WAIT_DATA, POST_ACK, WAIT_ACK, PUSH = 1, 2, 4, 8
+    buf = (C.c_int * (12 * 256))()
+    n = lib.b2c_debug_pass_plans(rows, cols, ch, 1, tb, strip, chunk, halo_depth, reps, 148, buf, 256)
+    assert 0 < n <= 256
+    passes = [list(buf[12 * i:12 * i + 12]) for i in range(n)]
+    out = (C.c_int * 10)()
+    lib.b2c_debug_band_plan(rows, cols, ch, 1, tb, strip, chunk, 0, 148, out)
+    bw = cols * ch
+    assert sum(p[0] for p in passes) == reps
+    group = []
+    for k, ext, mode, gend, prow, pbw, nbands, nchunks, chunk_rows, last, nbw, nbe in passes:
+        group.append((k, ext, mode))
+        xcol = -(-ext * ch // 16) * 16
+        assert prow == rows + 2 * ext and pbw == bw + 2 * xcol       # extended into the frame on all four sides
+        assert ext + k <= 32 and xcol + 32 <= 128                    # inside the 40-row / 128-byte frame
+        assert last == prow - (nchunks - 1) * chunk_rows
+        SB = 16 if strip == 0 else strip
+        if nchunks > 1:
+            # only the first / last chunk may touch frame rows: readers of the pass (k rows beyond the
+            # extended block) and, in the pushing pass, the F-deep ring
+            assert chunk_rows >= ext + k and last >= ext + k
+        if gend:
+            n_in = len(group)
+            assert ext == 0 and mode & PUSH
+            assert group[0][2] & WAIT_DATA
+            assert bool(mode & WAIT_ACK) == (n_in >= 2)
+            if n_in >= 2:
+                assert group[-2][2] & POST_ACK and group[-2][1] == k
+            assert sum(g[0] for g in group) <= 32
+            assert [g[1] for g in group] == [sum(x[0] for x in group[i + 1:]) for i in range(n_in)]
+            for g in group[:-1]:
+                assert not g[2] & PUSH
+            group = []
+    assert group == []
