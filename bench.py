@@ -50,6 +50,10 @@ def parse_args():
     ap.add_argument("--check-every", type=int, default=0)
     ap.add_argument("--weak", action="store_true", help="keep --width x --height per GPU (weak scaling)")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--halo-depth", type=int, default=0, help="iterations between two halo exchanges (0 = auto)")
+    ap.add_argument("--halo-prof", action="store_true", help="report the halo protocol's wait-time counters per rank")
+    ap.add_argument("--trace-e2e", action="store_true", help="report the per-image timeline of the end-to-end pipeline")
+    ap.add_argument("--no-solo", action="store_true", help="skip the block-alone diagnostic of multi-GPU runs")
     return ap.parse_args()
 
 
@@ -83,7 +87,7 @@ def run_b200conv(a):
     W, H = (weak_shape(world, a.width, a.height) if a.weak else (a.width, a.height))
     ch = 3 if a.color == "rgb" else 1
     opts = dict(boundary=a.boundary, tb=a.tb, strip_bytes=a.strip, chunk_rows=a.chunk_rows, kernel=a.kernel,
-                check_every=a.check_every)
+                check_every=a.check_every, halo_depth=a.halo_depth)
 
     if world > 1:
         eng = b200conv.ShardedBlur(W, H, ch, device=local, **opts)
@@ -128,12 +132,17 @@ def run_b200conv(a):
     for _ in range(a.warmup):
         core.run(a.reps)
     barrier()
+    if a.halo_prof and world > 1:
+        core.set_profile(True)
+        core.halo_profile(reset=True)
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     l0 = b200conv.total_launches()
     sampler = ClockSampler(local) if rank == 0 else None
     if sampler:
         sampler.__enter__()
     wall0 = time.perf_counter()
+    if world > 1:
+        core.barrier()      # device-side: every rank's timed region starts within microseconds
     ev0.record()
     for _ in range(a.steps):
         core.run(a.reps)
@@ -144,6 +153,18 @@ def run_b200conv(a):
         sampler.__exit__()
     ms = max_over_ranks(ev0.elapsed_time(ev1)) / a.steps
     launches = int(sum_over_ranks(b200conv.total_launches() - l0))
+    halo_prof = None
+    if a.halo_prof and world > 1:
+        hp = core.halo_profile(reset=True)
+        core.set_profile(False)
+        parts = [None] * world
+        dist.all_gather_object(parts, hp)
+        halo_prof = parts
+    start_wait = None
+    if world > 1:
+        parts = [None] * world
+        dist.all_gather_object(parts, core.barrier_wait_cycles())
+        start_wait = parts
     iters_done = core.iterations_done() if a.check_every else a.reps
     value = W * H * iters_done / (ms * 1e-3) / 1e9
 
@@ -179,7 +200,7 @@ def run_b200conv(a):
         # Several GPUs: the public streaming API (ShardedPipeline). Every step = H2D of each rank's
         # block from pinned memory + initial halo exchange + all iterations + D2H of the result;
         # the copies of neighbouring steps overlap the iterations (nothing is skipped or cached).
-        pipe = b200conv.ShardedPipeline(eng, a.reps, depth=2)
+        pipe = b200conv.ShardedPipeline(eng, a.reps, depth=2, trace=a.trace_e2e)
         outs = [host_out, torch.empty(shape, dtype=torch.uint8).pin_memory()]
         for i in range(max(2, min(a.warmup, 3))):
             pipe.submit(host_in, outs[i % 2])
@@ -196,8 +217,14 @@ def run_b200conv(a):
         e2e_wall = (time.perf_counter() - t0) / a.steps
         e2e_ms = max(max_over_ranks(e0.elapsed_time(e1)) / a.steps, 0.0)
         nbytes = int(host_in.numel())
+        timeline = None
+        if a.trace_e2e:
+            parts = [None] * world
+            dist.all_gather_object(parts, pipe.timeline()[-a.steps:])
+            timeline = parts
         e2e = {"value": W * H * a.reps / (e2e_ms * 1e-3) / 1e9, "unit": "Gpix-it/s",
                "ms_per_step": e2e_ms, "wall_ms_per_step": max_over_ranks(e2e_wall * 1e3),
+               "timeline_ms_per_rank": timeline,
                "timer": "CUDA events: before the first H2D .. after the last D2H, max over ranks",
                "api": "b200conv.ShardedPipeline(ShardedBlur, depth=2).submit(pinned_in, pinned_out)",
                "h2d_bytes_per_step": nbytes * world, "d2h_bytes_per_step": nbytes * world}
@@ -242,7 +269,7 @@ def run_b200conv(a):
         solo_ms = float("nan")
         try:
             m = re.search(r"strip=(\d+)B .*chunks=\d+\(x(\d+) rows\)", desc)
-            if m and not a.check_every:
+            if m and not a.check_every and not a.no_solo:
                 solo = b200conv.Engine(shape[1], shape[0], ch, device=local, boundary="zero", tb=a.tb, kernel=a.kernel,
                                        strip_bytes=int(m.group(1)), chunk_rows=int(m.group(2)))
                 solo.load(host_in)
@@ -287,6 +314,12 @@ def run_b200conv(a):
             "clocks": sampler.summary() if sampler else None,
             "e2e": e2e,
         }
+        if eng is not None and getattr(eng, "tuned", None):
+            out["config"]["coupled_tuning"] = eng.tuned
+        if start_wait is not None:
+            out["start_barrier_wait_cycles"] = start_wait
+        if halo_prof is not None:
+            out["halo_profile_per_rank"] = halo_prof
         if per_rank_ms is not None:
             clean = lambda v: [None if x != x else round(x, 4) for x in v]  # noqa: E731  (NaN -> null)
             out["per_rank"] = {"coupled_ms_per_step": clean(per_rank_ms),
@@ -339,40 +372,57 @@ def run_reference(a):
         rows = max(1, (64 << 20) // (W * ch))
         for r in range(0, H, rows):
             f.write(rng.integers(0, 256, size=(min(rows, H - r), W * ch), dtype=np.uint8).tobytes())
-    times, fail = [], None
+    times, failures = [], []
     env = dict(os.environ, CUDA_VISIBLE_DEVICES=os.environ.get("CUDA_VISIBLE_DEVICES", "0").split(",")[0])
     # Every step is a fresh process of the reference (context creation, PTX JIT from the compute
     # cache, file I/O), ~50 s each on the default config.  If warm-up + steps would run past the
-    # budget (B200CONV_REF_MAX_SECONDS, default 900), warm-ups are trimmed first (never below 1),
-    # then steps (never below 1); the JSON reports the counts actually run.
-    budget = float(os.environ.get("B200CONV_REF_MAX_SECONDS", "900"))
+    # budget (B200CONV_REF_MAX_SECONDS, default 540 — the driver gives each N 870 s), warm-ups are
+    # trimmed first (never below 1), then steps (never below 1); the JSON reports the counts
+    # actually run.  The reference reads and writes out of bounds in its rgb kernel
+    # (cuda/cuda_convolution.cu:34) and has been seen to die with "illegal memory access" on some
+    # boxes: a failed process is retried (same unmodified binary, same arguments, fresh process)
+    # up to 3 times in total per run of the arm, and every failure is reported.
+    budget = float(os.environ.get("B200CONV_REF_MAX_SECONDS", "540"))
+    max_failures = int(os.environ.get("B200CONV_REF_RETRIES", "3"))
     warmup, steps, trimmed = a.warmup, a.steps, False
     wall0 = time.perf_counter()
     i = 0
+    planned = False
     while i < warmup + steps:
+        left = budget - (time.perf_counter() - wall0)
         t_run = time.perf_counter()
-        p = subprocess.run([str(exe), "bench.raw", str(W), str(H), str(a.reps), a.color], cwd=tmp, env=env,
-                           capture_output=True, text=True)
+        try:
+            p = subprocess.run([str(exe), "bench.raw", str(W), str(H), str(a.reps), a.color], cwd=tmp, env=env,
+                               capture_output=True, text=True, timeout=max(60.0, left + 120.0))
+            rc_, so_, se_ = p.returncode, p.stdout, p.stderr
+        except subprocess.TimeoutExpired as te:
+            rc_, so_, se_ = 124, (te.stdout or b"").decode(errors="replace") if isinstance(te.stdout, bytes) else (te.stdout or ""), "timed out"
         t_run = time.perf_counter() - t_run
-        m = re.search(r"Execution time: ([0-9.]+) sec", p.stdout)
-        if p.returncode != 0 or not m:
-            fail = (p.stderr.strip() or p.stdout.strip() or f"exit {p.returncode}")[:300]
-            break
+        m = re.search(r"Execution time: ([0-9.]+) sec", so_)
+        if rc_ != 0 or not m:
+            failures.append((se_.strip() or so_.strip() or f"exit {rc_}")[:200])
+            if len(failures) >= max_failures or time.perf_counter() - wall0 > budget:
+                break
+            continue
         if i >= warmup:
             times.append(float(m.group(1)))
         i += 1
-        if i == 1:   # one run measured: does the plan fit the budget?
-            while warmup > 1 and t_run * (warmup + steps) > budget:
+        if not planned:   # one run measured: does the plan fit the budget?
+            planned = True
+            spent = time.perf_counter() - wall0
+            while warmup > 1 and spent + t_run * (warmup + steps - 1) > budget:
                 warmup, trimmed = warmup - 1, True
-            while steps > 1 and t_run * (warmup + steps) > budget:
+            while steps > 1 and spent + t_run * (warmup + steps - 1) > budget:
                 steps, trimmed = steps - 1, True
     wall = time.perf_counter() - wall0
     for f in tmp.iterdir():
         f.unlink()
     tmp.rmdir()
-    if fail is not None:
-        print(json.dumps({"impl": "reference", "unavailable": f"reference program failed: {fail}"}))
+    if not times:
+        print(json.dumps({"impl": "reference", "unavailable": "reference program failed "
+                          f"{len(failures)} time(s): " + " | ".join(failures)[:400], "failures": failures}))
         return
+    steps = len(times)
     sec = sum(times) / len(times)
     iters = 2 * (a.reps // 2)  # cuda_convolution.cu:93-97 copies back the wrong buffer for odd counts
     value = W * H * a.reps / sec / 1e9
@@ -382,6 +432,7 @@ def run_reference(a):
         "scaling": "weak" if a.weak else "strong", "vs_baseline": value / PUBLISHED[a.color],
         "dtype": "uint8 in/out, fp32+fp64 arithmetic", "data": "synthetic random uint8 .raw file",
         "impl": "reference", "requested": {"steps": a.steps, "warmup": a.warmup, "trimmed_to_time_budget": trimmed},
+        "retries": len(failures), "failures": failures,
         "config": {"model": f"3x3 gaussian blur {W}x{H} {a.color}", "width": W, "height": H, "color": a.color,
                    "repetitions": a.reps, "effective_iterations": iters,
                    "parallelism": "single GPU (the reference CUDA program cannot use more)",

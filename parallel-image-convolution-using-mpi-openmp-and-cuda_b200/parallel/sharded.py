@@ -143,7 +143,9 @@ class ShardedPipeline:
         pipe.wait()
     """
 
-    def __init__(self, sharded: ShardedBlur, repetitions: int, depth: int = 2):
+    def __init__(self, sharded: ShardedBlur, repetitions: int, depth: int = 2, trace: bool = False):
+        self.trace = bool(trace)
+        self._marks = []   # trace: per image {name: timing event}
         if int(sharded.engine.opts.check_every):
             raise ValueError("ShardedPipeline does not support check_every (the host must read the latch per image)")
         self.sharded = sharded
@@ -170,26 +172,52 @@ class ShardedPipeline:
         i = self._n % self.depth
         first_use = self._n < self.depth
         self._n += 1
+        marks = {}
+
+        def mark(name, stream):
+            if self.trace:
+                ev = torch.cuda.Event(enable_timing=True)
+                ev.record(stream)
+                marks[name] = ev
+
         with torch.cuda.device(self.sharded.device):
             if not first_use:
                 self.s_h2d.wait_event(self._in_free[i])
             with torch.cuda.stream(self.s_h2d):
+                mark("h2d_start", self.s_h2d)
                 self._in[i].copy_(src, non_blocking=True)
                 self._in_ready[i].record(self.s_h2d)
+                mark("h2d_end", self.s_h2d)
+            mark("compute_free", self.s_compute)   # the previous image's store has been issued before this
             self.s_compute.wait_event(self._in_ready[i])
             eng.load(self._in[i], stream=self.s_compute)
             self._in_free[i].record(self.s_compute)
             eng.exchange(stream=self.s_compute)
+            mark("run_start", self.s_compute)
             eng.run(self.repetitions, stream=self.s_compute)
+            mark("run_end", self.s_compute)
             if not first_use:
                 self.s_compute.wait_event(self._out_free[i])
             eng.store(self._out[i], stream=self.s_compute)
             self._out_ready[i].record(self.s_compute)
+            mark("store_end", self.s_compute)
             self.s_d2h.wait_event(self._out_ready[i])
             with torch.cuda.stream(self.s_d2h):
                 dst.copy_(self._out[i], non_blocking=True)
                 self._out_free[i].record(self.s_d2h)
+                mark("d2h_end", self.s_d2h)
+        if self.trace:
+            self._marks.append(marks)
 
     def wait(self):
         for s in (self.s_h2d, self.s_compute, self.s_d2h):
             s.synchronize()
+
+    def timeline(self):
+        """With ``trace=True``: per submitted image, milliseconds (device clock, relative to the first
+        image's upload start) at which each phase boundary passed on its stream."""
+        self.wait()
+        if not self._marks:
+            return []
+        t0 = self._marks[0]["h2d_start"]
+        return [{k: round(t0.elapsed_time(ev), 3) for k, ev in m.items()} for m in self._marks]

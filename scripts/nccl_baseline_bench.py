@@ -13,7 +13,7 @@ import torch.distributed as dist
 
 sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
 import b200conv  # noqa: E402
-from b200conv.parallel.nccl_baseline import NcclHaloBlur  # noqa: E402
+from b200conv.parallel.sendrecv import NcclHaloBlur  # noqa: E402
 
 ap = argparse.ArgumentParser()
 ap.add_argument("--width", type=int, default=16384)
