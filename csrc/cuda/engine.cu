@@ -54,10 +54,12 @@ constexpr int kPadBarrier = 704;      // kMaxRanks words: start-barrier sequence
 constexpr int kPadBarrierSkew = 768;  // 2 words (u64): cycles this rank waited in the last start barrier
 constexpr int kPadAcks = 1024;        // 8 x 32: ack epochs, index = direction of the acknowledging neighbour
 constexpr int kPadProf = 1280;        // 40 x u64 wait/publish counters (B200CONV_HALO_PROF=1)
+constexpr int kPadReady = 1408;       // 16 x 32: epochs handed to the courier (8 data, 8 ack)
 constexpr int kProfWords64 = 40;
 constexpr int kPadWords = 2048;
 static_assert(kPadSlots + 2 * kMaxRanks <= kPadChanged, "convergence slots overlap the next pad field");
-static_assert(kPadProf + 2 * kProfWords64 <= kPadWords, "profile counters overlap the end of the pad");
+static_assert(kPadProf + 2 * kProfWords64 <= kPadReady, "profile counters overlap the courier words");
+static_assert(kPadReady + 16 * 32 <= kPadWords, "courier words overlap the end of the pad");
 
 struct Blob {  // what b2c_engine_export ships; must fit B2C_HANDLE_BYTES
     cudaIpcMemHandle_t buf[2];
@@ -76,6 +78,20 @@ struct Pass {
     int ext;               // iterations left in the group after this pass = how far the block is extended
     int mode;              // kHalo* bits
     bool group_end;
+};
+
+// A run prepared for the persistent kernel: the leading passes with k == K as a device table,
+// the remainder (k < K at the end of a run) as ordinary launches.
+struct PersistPlan {
+    PassParams *d_passes = nullptr;
+    int *d_cum = nullptr;
+    uint32_t *d_counters = nullptr;   // per pass 8 x 32 arrival counters (passes overlap in time)
+    int npasses = 0;                  // passes in the table
+    long long items = 0;
+    int tstride = 0;
+    long long tile_words = 0;
+    uint32_t groups = 0;              // exchanges completed by the table's passes
+    std::vector<Pass> all;            // the whole run
 };
 
 struct BandPlan {
@@ -134,13 +150,39 @@ struct b2c_engine {
     uint32_t *res_flags = nullptr;   // sm_count x 32 words, then the error word
     uint32_t res_epoch = 0;
     mutable std::map<std::pair<int, int>, BandPlan> plan_cache;   // key (k, ext)
+    // persistent dataflow kernel: per (reps, cur) a device table of pass parameters
+    std::map<std::pair<int, int>, PersistPlan> persist;
+    uint32_t *tile_done = nullptr;       // per-tile "passes completed" words
+    long long tile_cap = 0;              // words allocated
+    unsigned long long *work_counter = nullptr;
+    unsigned long long item_base = 0;    // value of *work_counter once everything enqueued so far has run
+    uint32_t pass_base = 0;              // passes run through the persistent kernel so far
+    int persist_ctas = 0;
+    bool persist_auto = true;            // what "auto" means for this engine (block size / autotune)
+    // courier (kernels.cu): forwards halo epochs to peers on other devices from a side stream
+    bool remote_peers = false;           // some neighbour lives on another device
+    bool courier_on = false;             // the passes being enqueued hand their epochs to the courier
+    cudaStream_t side = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
 };
 
 namespace {
 
+// Forget everything that was built from the current plan or peer wiring (CUDA graphs, the
+// persistent kernel's pass tables).  The caller has made sure nothing of it is still running.
 void drop_graphs(b2c_engine *e) {
     for (auto &g : e->graphs) cudaGraphExecDestroy(g.second);
     e->graphs.clear();
+    if (!e->persist.empty()) {
+        cudaSetDevice(e->device);
+        cudaDeviceSynchronize();
+        for (auto &kv : e->persist) {
+            cudaFree(kv.second.d_passes);
+            cudaFree(kv.second.d_cum);
+            cudaFree(kv.second.d_counters);
+        }
+        e->persist.clear();
+    }
 }
 
 // Window geometry of a k-stage pass for the engine's strip width over a block `bw` bytes wide.
@@ -282,6 +324,8 @@ void fill_pass_params(const b2c_engine *e, const Pass &ps, int src_i, bool devic
     if (!h.enabled) return;
     h.mode = ps.mode;
     h.fused = (e->bw % e->SB == 0) ? 1 : 0;
+    static const int flag_fence = getenv("B200CONV_FLAG_FENCE") ? atoi(getenv("B200CONV_FLAG_FENCE")) : 1;
+    h.flag_fence = flag_fence;
     h.depth = e->F;
     h.epoch = device_epoch ? e->epoch - e->epoch_dev : e->epoch;
     h.epoch_base = device_epoch ? e->pad + kPadEpoch : nullptr;
@@ -289,6 +333,7 @@ void fill_pass_params(const b2c_engine *e, const Pass &ps, int src_i, bool devic
     h.acks = e->pad + kPadAcks;
     h.counters = e->pad + kPadCounters;
     h.prof = e->prof ? reinterpret_cast<unsigned long long *>(e->pad + kPadProf) : nullptr;
+    h.ready = e->courier_on && h.fused ? e->pad + kPadReady : nullptr;
     h.delay = e->delay;
     const int exp[8] = {bp.nbands, bp.nbands, bp.nbw * bp.nchunks, bp.nbe * bp.nchunks,
                         bp.nbw, bp.nbe, bp.nbw, bp.nbe};
@@ -417,6 +462,188 @@ int enqueue_pass(b2c_engine *e, const Pass &ps, bool device_epoch, cudaStream_t 
     return B2C_OK;
 }
 
+int enqueue_epoch_sync(b2c_engine *e, bool device_epoch, cudaStream_t s);
+
+// Peers on other devices: the flag stores need system scope, and that fence is kept out of the
+// passes (halo_publish in stencil_stream.cuh) by a courier kernel on a side stream.
+bool want_courier(const b2c_engine *e) {
+    static const bool off = getenv("B200CONV_COURIER") && atoi(getenv("B200CONV_COURIER")) == 0;
+    // not with check_every: after the convergence latch the passes publish nothing and the courier would wait for ever
+    return !off && e->any_nb && e->remote_peers && e->kernel != B2C_KERNEL_NAIVE && e->bw % e->SB == 0 &&
+           e->opts.check_every == 0;
+}
+
+// Forks the courier off stream s for the passes that follow (which must all be enqueued before
+// courier_end).  Works inside a stream capture: the side stream joins the capture through the event.
+int courier_begin(b2c_engine *e, const std::vector<Pass> &passes, bool device_epoch, cudaStream_t s) {
+    e->courier_on = false;
+    if (!want_courier(e) || !s) return B2C_OK;   // not beside the legacy default stream
+    uint32_t groups = 0, ack_group = 0;
+    bool has_ack = false;
+    for (const Pass &ps : passes) {
+        if (ps.mode & kHaloPostAck) { has_ack = true; ack_group = groups; }
+        if (ps.group_end) groups++;
+    }
+    if (groups == 0) return B2C_OK;
+    if (!e->side) {
+        CK(cudaStreamCreateWithFlags(&e->side, cudaStreamNonBlocking));
+        CK(cudaEventCreateWithFlags(&e->ev_fork, cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&e->ev_join, cudaEventDisableTiming));
+    }
+    CourierParams c{};
+    c.ready = e->pad + kPadReady;
+    for (int d = 0; d < 8; ++d) {
+        if (e->nb[d] < 0) continue;
+        c.peer_flag[d] = e->peer_pad[d] + kPadFlags + opposite_dir(d) * 32;
+        c.peer_ack[d] = e->peer_pad[d] + kPadAcks + opposite_dir(d) * 32;
+    }
+    const uint32_t rel = device_epoch ? e->epoch - e->epoch_dev : e->epoch;
+    c.epoch_base = device_epoch ? e->pad + kPadEpoch : nullptr;
+    c.start_epoch = rel;
+    c.final_data = rel + groups;
+    c.final_ack = rel + ack_group;
+    c.has_ack = has_ack ? 1 : 0;
+    CK(cudaEventRecord(e->ev_fork, s));
+    CK(cudaStreamWaitEvent(e->side, e->ev_fork, 0));
+    CK(launch_courier(c, e->side));
+    e->launches++;
+    e->courier_on = true;
+    return B2C_OK;
+}
+
+int courier_end(b2c_engine *e, cudaStream_t s) {
+    if (!e->courier_on) return B2C_OK;
+    e->courier_on = false;
+    CK(cudaEventRecord(e->ev_join, e->side));
+    CK(cudaStreamWaitEvent(s, e->ev_join, 0));
+    return B2C_OK;
+}
+
+bool persist_enabled(const b2c_engine *e) {
+    static const int env = getenv("B200CONV_PERSIST") ? atoi(getenv("B200CONV_PERSIST")) : -1;
+    const int want = e->opts.persistent >= 0 ? e->opts.persistent : env;
+    if (want == 0 || (want < 0 && !e->persist_auto)) return false;
+    if (e->kernel != B2C_KERNEL_STREAM || e->opts.check_every > 0 || e->opts.boundary == B2C_CUDA_COMPAT) return false;
+    if (e->any_nb && e->bw % e->SB != 0) return false;   // the ring would need halo_push_kernel between passes
+    return true;
+}
+
+// Builds (or finds) the pass table of a `reps`-iteration run that starts on buffer e->cur.
+int persist_plan(b2c_engine *e, int reps, PersistPlan **out) {
+    const auto key = std::make_pair(reps, e->cur);
+    auto it = e->persist.find(key);
+    if (it != e->persist.end()) {
+        *out = &it->second;
+        return B2C_OK;
+    }
+    if (e->persist.size() >= 16) drop_graphs(e);
+    PersistPlan pl;
+    pl.all = make_passes(e, reps);
+    while (pl.npasses < (int)pl.all.size() && pl.all[(size_t)pl.npasses].k == e->K) pl.npasses++;
+    if (pl.npasses > 0) {
+        const size_t np = (size_t)pl.npasses;
+        CK(cudaMalloc(&pl.d_counters, np * 256 * sizeof(uint32_t)));
+        CK(cudaMemset(pl.d_counters, 0, np * 256 * sizeof(uint32_t)));
+        std::vector<PassParams> tab(np);
+        std::vector<int> cum(np + 1, 0);
+        // walk the passes with the host state a real run would have; epochs come out relative to the start
+        const int cur0 = e->cur;
+        const uint32_t epoch0 = e->epoch, dev0 = e->epoch_dev;
+        e->epoch_dev = e->epoch;
+        const bool courier0 = e->courier_on;
+        e->courier_on = want_courier(e);
+        int max_nb = 1, max_nc = 1;
+        for (size_t t = 0; t < np; ++t) {
+            const Pass &ps = pl.all[t];
+            PassParams &p = tab[t];
+            fill_pass_params(e, ps, e->cur, true, p);
+            p.halo.epoch_base = nullptr;   // the kernel adds the epoch at launch
+            p.halo.counters = pl.d_counters + t * 256;
+            p.raster = (!e->any_nb || !(ps.mode & (kHaloPush | kHaloPostAck))) ? 1 : 0;
+            cum[t + 1] = cum[t] + p.nbands * p.nchunks;
+            max_nb = std::max(max_nb, p.nbands);
+            max_nc = std::max(max_nc, p.nchunks);
+            e->cur ^= 1;
+            if (e->any_nb && ps.group_end) { e->epoch++; pl.groups++; }
+        }
+        e->cur = cur0;
+        e->epoch = epoch0;
+        e->epoch_dev = dev0;
+        e->courier_on = courier0;
+        pl.items = cum[np];
+        pl.tstride = max_nb;
+        pl.tile_words = (long long)max_nb * max_nc;
+        CK(cudaMalloc(&pl.d_passes, np * sizeof(PassParams)));
+        CK(cudaMalloc(&pl.d_cum, (np + 1) * sizeof(int)));
+        CK(cudaMemcpy(pl.d_passes, tab.data(), np * sizeof(PassParams), cudaMemcpyHostToDevice));
+        CK(cudaMemcpy(pl.d_cum, cum.data(), (np + 1) * sizeof(int), cudaMemcpyHostToDevice));
+    }
+    *out = &e->persist.emplace(key, std::move(pl)).first->second;
+    return B2C_OK;
+}
+
+int run_persistent(b2c_engine *e, int reps, cudaStream_t s) {
+    PersistPlan *pl = nullptr;
+    int rc = persist_plan(e, reps, &pl);
+    if (rc != B2C_OK) return rc;
+    if (pl->npasses > 0) {
+        if (!e->work_counter) {
+            CK(cudaMalloc(&e->work_counter, 8 * sizeof(unsigned long long)));   // [0] counter, [1..5] profile
+            CK(cudaMemset(e->work_counter, 0, 8 * sizeof(unsigned long long)));
+            e->item_base = 0;
+        }
+        if (pl->tile_words > e->tile_cap) {
+            CK(cudaDeviceSynchronize());   // nobody may still be reading the old words
+            if (e->tile_done) cudaFree(e->tile_done);
+            e->tile_done = nullptr;
+            e->tile_cap = 0;
+            CK(cudaMalloc(&e->tile_done, (size_t)pl->tile_words * sizeof(uint32_t)));
+            // any value not above pass_base reads as "not done yet"
+            CK(cudaMemset(e->tile_done, 0, (size_t)pl->tile_words * sizeof(uint32_t)));
+            if (e->pass_base > 0) {
+                std::vector<uint32_t> init((size_t)pl->tile_words, e->pass_base);
+                CK(cudaMemcpy(e->tile_done, init.data(), init.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+            }
+            e->tile_cap = pl->tile_words;
+        }
+        if (!e->persist_ctas) {
+            int occ = stream_persist_occupancy(e->K, e->SB, e->CH);
+            if (occ <= 0) occ = 1;
+            e->persist_ctas = occ * e->sm_count;
+        }
+    }
+    // every allocation (and the synchronisation that may come with it) is behind us: the courier
+    // waits for epochs that only the launches below produce
+    if ((rc = courier_begin(e, pl->all, false, s)) != B2C_OK) return rc;
+    if (pl->npasses > 0) {
+        PersistParams q{};
+        q.passes = pl->d_passes;
+        q.cum = pl->d_cum;
+        q.npasses = pl->npasses;
+        q.counter = e->work_counter;
+        q.item_base = e->item_base;
+        q.tile_done = e->tile_done;
+        q.tstride = pl->tstride;
+        q.pass_base = e->pass_base;
+        q.epoch0 = e->epoch;
+        // B200CONV_PERSIST_PROF=1: where the persistent kernel's warps spend their cycles (5 words behind the counter)
+        static const bool pprof = getenv("B200CONV_PERSIST_PROF") && atoi(getenv("B200CONV_PERSIST_PROF")) != 0;
+        q.prof = pprof ? e->work_counter + 1 : nullptr;
+        const int ctas = (int)std::min<long long>(e->persist_ctas, ceil_div(pl->items, kWarpsPerCta));
+        CK(launch_stream_persist(q, e->K, e->SB, e->CH, ctas, s));
+        e->launches++;
+        // every warp of the grid leaves after exactly one fetch past the end
+        e->item_base += (unsigned long long)pl->items + (unsigned long long)ctas * kWarpsPerCta;
+        e->pass_base += (uint32_t)pl->npasses;
+        e->cur ^= pl->npasses & 1;
+        e->epoch += pl->groups;
+    }
+    for (size_t t = (size_t)pl->npasses; t < pl->all.size(); ++t)   // k < K at the end of the run
+        if ((rc = enqueue_pass(e, pl->all[t], false, s)) != B2C_OK) return rc;
+    if ((rc = courier_end(e, s)) != B2C_OK) return rc;
+    return enqueue_epoch_sync(e, false, s);
+}
+
 // After the last pass of a run the device-side epoch word catches up with the host's count.
 int enqueue_epoch_sync(b2c_engine *e, bool device_epoch, cudaStream_t s) {
     if (!e->any_nb || e->kernel == B2C_KERNEL_NAIVE) { e->epoch_dev = e->epoch; return B2C_OK; }
@@ -446,6 +673,12 @@ void choose_plan(b2c_engine *e) {
     e->F = e->any_nb ? K : 1;
     if (e->kernel == B2C_KERNEL_NAIVE) e->F = 1;
     e->chunk_rows_fixed = o.chunk_rows > 0;
+    // The persistent kernel needs well over two waves of work items per pass: an item may start
+    // when its nine predecessors of the pass before are done, a warp whose item is not ready yet
+    // just waits, and with fewer items per pass than that the slow edge tiles of consecutive passes
+    // form the critical path (measured: profiles/persist_sweep.txt).  Smaller blocks keep one launch
+    // per pass (single-rank engines measure both in autotune_chunk_rows instead).
+    e->persist_auto = (double)e->bw * e->R >= 300e6;
     int SB = o.strip_bytes;
     if (SB != 4 && SB != 8 && SB != 16) {
         // strip width with the lowest modelled pass time (see plan_cost)
@@ -489,6 +722,8 @@ void choose_plan(b2c_engine *e) {
 // all-zero) buffers with the halo logic off: the kernel's time does not depend on pixel values,
 // zeros blur to zeros, and no frame or flag is touched.  ~10 ms once per engine; set
 // B200CONV_AUTOTUNE=0 or give chunk_rows explicitly to skip it.
+int run_streaming(b2c_engine *e, int reps, cudaStream_t s);
+
 int autotune_chunk_rows(b2c_engine *e) {
     static const bool off = getenv("B200CONV_AUTOTUNE") && atoi(getenv("B200CONV_AUTOTUNE")) == 0;
     if (off || e->opts.chunk_rows > 0) return B2C_OK;
@@ -503,6 +738,8 @@ int autotune_chunk_rows(b2c_engine *e) {
     static const int cand[] = {8, 12, 16, 24, 32, 48, 64, 80, 96, 112, 128, 144, 160, 192};
     const bool any_nb = e->any_nb;
     e->any_nb = false;
+    const int use_graph = e->opts.use_graph;
+    e->opts.use_graph = 0;
     cudaStream_t s = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     int rc = B2C_OK, best = 0;
@@ -514,6 +751,11 @@ int autotune_chunk_rows(b2c_engine *e) {
     }
     const int sb0 = e->SB;
     int best_sb = sb0;
+    bool best_pm = e->persist_auto;
+    const bool pm_open = e->opts.persistent < 0 && !getenv("B200CONV_PERSIST") && bytes >= 32e6 && bytes < 300e6;
+    for (int pm = 1; pm >= 0 && rc == B2C_OK; --pm) {
+    if (pm_open) e->persist_auto = pm != 0;
+    else if (pm == 0) break;
     for (int sb = 16; sb >= (bytes < 64e6 ? 4 : 8) && rc == B2C_OK; sb >>= 1) {
         // also try the other strip width unless the caller fixed it (K*words <= 16 registers budget)
         if (sb != sb0 && (e->opts.strip_bytes > 0 || e->K * (sb / 4) > 16)) continue;
@@ -525,35 +767,36 @@ int autotune_chunk_rows(b2c_engine *e) {
             if (c > 48 && bytes < 16e6) continue;                         // and long chunks starve small ones
             e->opts.chunk_rows = c;
             e->plan_cache.clear();
-            PassParams p;
-            Pass ps{};
-            ps.k = e->K;
-            fill_pass_params(e, ps, 0, false, p);
-            cudaError_t ce = cudaSuccess;
-            const int reps = bytes < 16e6 ? 41 : (bytes < 128e6 ? 9 : 3);   // short passes: average more of them
-            for (int it = 0; it < reps && ce == cudaSuccess; ++it) {
-                if (it == 1) cudaEventRecord(ev0, s);
-                ce = e->kernel == B2C_KERNEL_TMA ? launch_stream_tma(e->tma, p, 0, e->K, e->SB, e->CH, false, s)
-                                                 : launch_stream(p, e->K, e->SB, e->CH, false, s);
-            }
+            drop_graphs(e);
+            // the path a real run takes (persistent kernel or one launch per pass), once to warm up
+            // and build its tables, once timed
+            const int passes = bytes < 16e6 ? 40 : (bytes < 128e6 ? 8 : 3);   // short passes: average more of them
+            int rr = run_streaming(e, passes * e->K, s);
+            cudaEventRecord(ev0, s);
+            if (rr == B2C_OK) rr = run_streaming(e, passes * e->K, s);
             cudaEventRecord(ev1, s);
-            if (ce != cudaSuccess || cudaEventSynchronize(ev1) != cudaSuccess) {
-                set_error("autotune: %s", cudaGetErrorString(cudaGetLastError()));
+            if (rr != B2C_OK || cudaEventSynchronize(ev1) != cudaSuccess) {
+                if (rr == B2C_OK) set_error("autotune: %s", cudaGetErrorString(cudaGetLastError()));
                 rc = B2C_ECUDA;
                 break;
             }
             float ms = 0.f;
             cudaEventElapsedTime(&ms, ev0, ev1);
-            if (ms < best_ms) { best_ms = ms; best = c; best_sb = sb; }
+            if (ms < best_ms) { best_ms = ms; best = c; best_sb = sb; best_pm = e->persist_auto; }
         }
     }
+    }
     e->SB = best_sb;
+    e->persist_auto = best_pm;
     if (ev0) cudaEventDestroy(ev0);
     if (ev1) cudaEventDestroy(ev1);
     if (s) cudaStreamDestroy(s);
     e->any_nb = any_nb;
     e->opts.chunk_rows = best;   // 0 (model) when nothing was timed
+    e->opts.use_graph = use_graph;
     e->plan_cache.clear();
+    drop_graphs(e);
+    e->cur = 0;
     return rc;
 }
 
@@ -591,6 +834,7 @@ void b2c_default_opts(b2c_opts *o) {
     o->kernel = B2C_KERNEL_AUTO;
     o->use_graph = -1;
     o->halo_depth = 0;
+    o->persistent = -1;
 }
 
 b2c_engine *b2c_engine_create(int device, int W, int H, int CH, int P, int Q, int rank, const b2c_opts *opts) {
@@ -703,7 +947,12 @@ void b2c_engine_destroy(b2c_engine *e) {
     if (!e) return;
     cudaSetDevice(e->device);
     cudaDeviceSynchronize();
-    for (auto &g : e->graphs) cudaGraphExecDestroy(g.second);
+    drop_graphs(e);
+    if (e->tile_done) cudaFree(e->tile_done);
+    if (e->work_counter) cudaFree(e->work_counter);
+    if (e->side) cudaStreamDestroy(e->side);
+    if (e->ev_fork) cudaEventDestroy(e->ev_fork);
+    if (e->ev_join) cudaEventDestroy(e->ev_join);
     for (void *p : e->ipc_opened) cudaIpcCloseMemHandle(p);
     if (e->tma) tma_destroy(e->tma);
     for (auto &b : e->res_xbuf) if (b) cudaFree(b);
@@ -787,6 +1036,7 @@ int b2c_engine_import(b2c_engine *e, const void *blobs, int n) {
         e->peer_pad[d] = e->rank_pad[k];
     }
     e->connected = true;
+    e->remote_peers = n > 1;
     drop_graphs(e);
     return B2C_OK;
 }
@@ -802,6 +1052,7 @@ int b2c_engine_disconnect(b2c_engine *e) {
     memset(e->peer_pad, 0, sizeof e->peer_pad);
     memset(e->rank_pad, 0, sizeof e->rank_pad);
     e->connected = false;
+    e->remote_peers = false;
     return B2C_OK;
 }
 
@@ -832,6 +1083,7 @@ int b2c_engine_connect_local(b2c_engine **engines, int n) {
             e->peer_base[0][d] = engines[k]->base[0];
             e->peer_base[1][d] = engines[k]->base[1];
             e->peer_pad[d] = engines[k]->pad;
+            if (engines[k]->device != e->device) e->remote_peers = true;
         }
         e->connected = true;
         drop_graphs(e);
@@ -959,6 +1211,20 @@ int b2c_engine_run(b2c_engine *e, int reps, void *stream) {
         e->cur ^= 1;
         return B2C_OK;
     }
+    return run_streaming(e, reps, s);
+}
+
+}  // extern "C"
+
+namespace {
+
+// The iteration loop of the streaming kernels: one persistent kernel, or one launch per pass
+// (replayed as a CUDA graph when the run is long enough).
+int run_streaming(b2c_engine *e, int reps, cudaStream_t s) {
+    if (persist_enabled(e) && !(want_courier(e) && !s)) {   // the courier cannot run beside the legacy default stream
+        e->iters_done = reps;
+        return run_persistent(e, reps, s);
+    }
     const std::vector<Pass> passes = make_passes(e, reps);
     e->iters_done = reps;
     // Epochs come from a device word plus a per-pass offset, so a run is the same sequence of
@@ -992,9 +1258,10 @@ int b2c_engine_run(b2c_engine *e, int reps, void *stream) {
             const long long l0 = e->launches, g0 = total_launches();
             cudaGraph_t g;
             CK(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
-            int rc = B2C_OK;
+            int rc = courier_begin(e, passes, true, s);
             for (const Pass &ps : passes)
-                if ((rc = enqueue_pass(e, ps, true, s)) != B2C_OK) break;
+                if (rc != B2C_OK || (rc = enqueue_pass(e, ps, true, s)) != B2C_OK) break;
+            if (rc == B2C_OK) rc = courier_end(e, s);
             if (rc == B2C_OK) rc = enqueue_epoch_sync(e, true, s);
             cudaError_t ce = cudaStreamEndCapture(s, &g);
             e->cur = cur0;
@@ -1020,18 +1287,22 @@ int b2c_engine_run(b2c_engine *e, int reps, void *stream) {
             if (e->any_nb && ps.group_end) groups++;
             if (e->any_nb && (ps.mode & kHaloPush) && e->bw % e->SB != 0) nodes++;
         }
-        if (groups) nodes++;
+        if (groups) nodes += want_courier(e) ? 2 : 1;
         count_launch(nodes);
         e->cur ^= (int)(passes.size() & 1);
         e->epoch = e->epoch_dev = epoch0 + groups;
         return B2C_OK;
     }
-    for (const Pass &ps : passes) {
-        int rc = enqueue_pass(e, ps, device_epoch, s);
-        if (rc != B2C_OK) return rc;
-    }
+    int rc = courier_begin(e, passes, device_epoch, s);
+    for (const Pass &ps : passes)
+        if (rc != B2C_OK || (rc = enqueue_pass(e, ps, device_epoch, s)) != B2C_OK) return rc;
+    if ((rc = courier_end(e, s)) != B2C_OK) return rc;
     return enqueue_epoch_sync(e, device_epoch, s);
 }
+
+}  // namespace
+
+extern "C" {
 
 // Pass-by-pass variant of b2c_engine_run for callers that interleave several engines on ONE
 // device (the sequential multi-rank emulation of the tests): plan_run fixes the pass list,
@@ -1104,7 +1375,8 @@ int64_t b2c_engine_launches(const b2c_engine *e) { return e ? e->launches : 0; }
 
 int b2c_engine_describe(const b2c_engine *e, char *buf, size_t buflen) {
     if (!e || !buf) return B2C_EINVAL;
-    const char *kn = e->kernel == B2C_KERNEL_NAIVE ? "naive" : (e->kernel == B2C_KERNEL_TMA ? "tma" : "stream");
+    const char *kn = e->kernel == B2C_KERNEL_NAIVE ? "naive" : (e->kernel == B2C_KERNEL_TMA ? "tma" :
+                     (persist_enabled(e) ? "stream-persistent" : "stream"));
     if (e->opts.boundary == B2C_CUDA_COMPAT) {
         snprintf(buf, buflen, "kernel=compat W=%d H=%d CH=%d", e->W, e->H, e->CH);
         return B2C_OK;
@@ -1274,6 +1546,19 @@ int64_t b2c_engine_barrier_wait_cycles(b2c_engine *e) {
     unsigned long long v = 0;
     CK(cudaMemcpy(&v, e->pad + kPadBarrierSkew, sizeof v, cudaMemcpyDeviceToHost));
     return (int64_t)v;
+}
+
+// B200CONV_PERSIST_PROF=1: cycles summed over the persistent kernel's warps since the last call:
+// {waiting for tiles, inside tiles, total, items, items that had to wait}.
+int b2c_engine_persist_profile(b2c_engine *e, uint64_t out[5]) {
+    if (!e || !out) return B2C_EINVAL;
+    memset(out, 0, 5 * sizeof(uint64_t));
+    if (!e->work_counter) return B2C_OK;
+    CK(cudaSetDevice(e->device));
+    CK(cudaDeviceSynchronize());
+    CK(cudaMemcpy(out, e->work_counter + 1, 5 * sizeof(uint64_t), cudaMemcpyDeviceToHost));
+    CK(cudaMemset(e->work_counter + 1, 0, 5 * sizeof(uint64_t)));
+    return B2C_OK;
 }
 
 int b2c_engine_set_profile(b2c_engine *e, int on) {

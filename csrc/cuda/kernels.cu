@@ -80,6 +80,42 @@ int stream_occupancy(int k, int strip_bytes, int ch) {
     return occ;
 }
 
+// -------------------------------------------------------------- persistent
+
+template <int K, int NW, int CH>
+static cudaError_t persist_op_t(int op, const PersistParams *q, int ctas, cudaStream_t s, int *occ) {
+    auto fn = stream_persist_kernel<K, NW, CH>;
+    if (op == 1) return cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, fn, kWarpsPerCta * 32, 0);
+    fn<<<ctas, kWarpsPerCta * 32, 0, s>>>(*q);
+    count_launch(1);
+    return cudaGetLastError();
+}
+
+static cudaError_t persist_op(int op, const PersistParams *q, int k, int strip_bytes, int ch, int ctas, cudaStream_t s,
+                              int *occ) {
+#define B2C_CASE(K_, NW_)                                                              \
+    if (k == K_ && strip_bytes == NW_ * 4)                                             \
+        return ch == 1 ? persist_op_t<K_, NW_, 1>(op, q, ctas, s, occ) : persist_op_t<K_, NW_, 3>(op, q, ctas, s, occ);
+    B2C_CASE(1, 1) B2C_CASE(2, 1) B2C_CASE(4, 1) B2C_CASE(8, 1)
+    B2C_CASE(1, 2) B2C_CASE(2, 2) B2C_CASE(4, 2) B2C_CASE(8, 2)
+    B2C_CASE(1, 4) B2C_CASE(2, 4) B2C_CASE(4, 4)
+#undef B2C_CASE
+    return cudaErrorInvalidValue;
+}
+
+cudaError_t launch_stream_persist(const PersistParams &q, int k, int strip_bytes, int ch, int ctas, cudaStream_t s) {
+    return persist_op(0, &q, k, strip_bytes, ch, ctas, s, nullptr);
+}
+
+int stream_persist_occupancy(int k, int strip_bytes, int ch) {
+    int occ = 0;
+    if (persist_op(1, nullptr, k, strip_bytes, ch, 0, nullptr, &occ) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return occ;
+}
+
 // ------------------------------------------------------------------- naive
 
 // One iteration, one thread per output byte, on the engine's framed buffers.
@@ -333,6 +369,40 @@ __global__ void barrier_kernel(const BarrierParams b) {
     }
     __syncwarp();
     if (lane == 0 && b.skew_cycles) *b.skew_cycles = (unsigned long long)(clock64() - t0);
+}
+
+__global__ void courier_kernel(const CourierParams c) {
+    const int lane = threadIdx.x;
+    const int d = lane & 7;
+    const bool ack = lane >= 8;
+    uint32_t *const dst = ack ? c.peer_ack[d] : c.peer_flag[d];
+    if (lane >= 16 || !dst || (ack && !c.has_ack)) return;
+    const uint32_t base = c.epoch_base ? __ldcg(c.epoch_base) : 0u;
+    const uint32_t last = base + (ack ? c.final_ack : c.final_data);
+    uint32_t sent = base + c.start_epoch - (ack ? 1u : 0u);   // acks carry the epoch of their own group
+    const uint32_t *const src = c.ready + lane * 32;
+    long long t0 = clock64();
+    while ((int)(sent - last) < 0) {
+        const uint32_t v = ld_acquire_gpu(src);
+        if ((int)(v - sent) > 0 && (int)(v - last) <= 0) {
+            __threadfence_system();    // fence.sc.sys: cumulative over the ring warps' stores
+            st_release_sys(dst, v);
+            sent = v;
+            t0 = clock64();
+        } else {
+            __nanosleep(200);
+            if (clock64() - t0 > (40ll << 30)) {
+                printf("b200conv: courier timeout dir=%d %s sent=%u last=%u ready=%u\n", d, ack ? "ack" : "data", sent, last, v);
+                __trap();
+            }
+        }
+    }
+}
+
+cudaError_t launch_courier(const CourierParams &c, cudaStream_t s) {
+    courier_kernel<<<1, 32, 0, s>>>(c);
+    count_launch(1);
+    return cudaGetLastError();
 }
 
 cudaError_t launch_barrier(const BarrierParams &b, cudaStream_t s) {

@@ -7,6 +7,7 @@
 namespace b2c {
 
 struct PassParams;
+struct PersistParams;
 
 struct NaiveWeights {
     int iw[3][3];
@@ -49,6 +50,9 @@ __host__ __device__ inline int kDirDcDev(int d) { return d == 2 || d == 4 || d =
 bool stream_config_ok(int k, int strip_bytes);
 int stream_occupancy(int k, int strip_bytes, int ch);  // resident CTAs (of kWarpsPerCta warps) per SM
 cudaError_t launch_stream(const PassParams &p, int k, int strip_bytes, int ch, bool check, cudaStream_t s);
+// Persistent dataflow kernel (stencil_stream.cuh): every pass of a run in one launch of `ctas` CTAs.
+cudaError_t launch_stream_persist(const PersistParams &q, int k, int strip_bytes, int ch, int ctas, cudaStream_t s);
+int stream_persist_occupancy(int k, int strip_bytes, int ch);
 cudaError_t launch_naive(const uint8_t *src, uint8_t *dst, long long pitch, int rows, int bw, int ch,
                          const NaiveWeights &w, cudaStream_t s);
 cudaError_t launch_compat(const uint8_t *src, uint8_t *dst, int W, int H, int ch, cudaStream_t s);
@@ -67,6 +71,21 @@ struct BarrierParams {
     unsigned long long *skew_cycles;  // optional: cycles this rank spent waiting (written by lane 0)
 };
 cudaError_t launch_barrier(const BarrierParams &b, cudaStream_t s);
+
+// Courier: one warp that lives beside a run and forwards halo epochs from local "ready" words to
+// the neighbours' flag / ack words with system-scope ordering (lane d: data flag of direction d,
+// lane 8+d: ack of direction d).  It leaves when the last epoch of the run has been forwarded.
+struct CourierParams {
+    const uint32_t *ready;        // [16][32] words
+    uint32_t *peer_flag[8];
+    uint32_t *peer_ack[8];
+    const uint32_t *epoch_base;   // added to the three values below (null: 0)
+    uint32_t start_epoch;         // data epochs up to this one are already published
+    uint32_t final_data;          // last data epoch of the run
+    uint32_t final_ack;           // last ack epoch of the run
+    int has_ack;                  // 0: no group of the run acknowledges
+};
+cudaError_t launch_courier(const CourierParams &c, cudaStream_t s);
 
 long long total_launches();
 void count_launch(long long n);

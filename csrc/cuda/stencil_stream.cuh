@@ -61,6 +61,8 @@ struct HaloParams {
     int enabled;            // any neighbour at all
     int mode;               // kHalo* bits of this pass
     int fused;              // 1: kHaloPush stores come from this kernel (aligned widths); 0: halo_push_kernel follows
+    int flag_fence;         // how the last arriver orders the ring before the flag: 0 fence.sc.sys + st.release.sys,
+                            // 1 st.release.sys alone (default), 2 fence.acq_rel.gpu + st.relaxed.sys (experiment)
     int depth;              // ring depth F (rows, and F*CH byte columns)
     uint32_t epoch;         // group epoch E, relative to *epoch_base: data/ack flags must be >= E, E+1 is published
     const uint32_t *epoch_base;  // device word holding the epoch at the start of the run (null: 0)
@@ -70,13 +72,15 @@ struct HaloParams {
     uint32_t *flags;        // our data-flag words, index = direction the data came from
     uint32_t *acks;         // our ack words, index = direction of the neighbour that acknowledged
     uint32_t *counters;     // our per-direction arrival counters
+    uint32_t *ready;        // when set: the last arriver only stores the epoch here (index d*32 data, (8+d)*32 ack,
+                            // GPU scope) and the courier kernel forwards it to the neighbour (see kernels.cu)
     unsigned long long *prof;  // opt-in wait/publish cycle counters (null: off), layout in engine.cu
     int expected[8];        // ring warps per direction
     int nbw, nbe;           // bands holding the west / east ring
     long long delay;        // test hook: spin this many clocks before each wait
 };
 
-struct PassParams {
+struct alignas(16) PassParams {
     const uint8_t *src;  // interior origin of the source buffer
     uint8_t *dst;        // interior origin of the destination buffer
     long long pitch;
@@ -89,6 +93,7 @@ struct PassParams {
     unsigned int *changed;  // CHECK: OR-accumulated "last stage changed a byte"
     const unsigned int *converged;  // when set (non-null and non-zero) the pass is skipped
     int org_x, org_y;       // position of src/dst (0,0) inside the allocation (bytes, rows): TMA coordinates
+    int raster;             // 1: chunk-major work order instead of ring-first
 #ifdef B2C_DEBUG
     const uint8_t *dbg_src_lo, *dbg_src_hi;   // [lo, hi) of the source / destination allocation
     uint8_t *dbg_dst_lo, *dbg_dst_hi;
@@ -408,10 +413,12 @@ __device__ __forceinline__ void stream_band(const PassParams &p, Feed &feed, con
     }
 }
 
-// Ring-first work order: top chunk, bottom chunk, then the west/east bands of
-// the middle chunks, then the interior.
+// Work order of a pass.  Ring-first (passes that push or acknowledge): top chunk, bottom chunk,
+// then the west/east bands of the middle chunks, then the interior — so the neighbours get their
+// epoch early.  Raster (every other pass): chunk-major, which is the order in which the
+// persistent kernel's tile dependencies resolve without waiting.
 __host__ __device__ __forceinline__ void map_work(int id, int NB, int NC, int nbw, int nbe, int &band, int &chunk) {
-    if (NC <= 2 || NB <= nbw + nbe) {  // everything is ring
+    if (NC <= 2 || NB <= nbw + nbe) {  // everything is ring (or raster was asked for: nbw = NB)
         chunk = id / NB; band = id % NB; return;
     }
     if (id < NB) { chunk = 0; band = id; return; }
@@ -506,21 +513,41 @@ __device__ __forceinline__ void halo_wait(const HaloParams &h, const unsigned dm
 }
 
 // Ring warps after their band: every lane's remote stores are issued; lanes 0-7 each take one
-// direction, make the warp's stores visible system-wide, count in, and the last arriver of a
-// direction publishes the epoch (data: E+1 into the neighbour's flag; ack: E into its ack word).
+// direction, order the warp's stores before the count-in, and the last arriver of a direction
+// publishes the epoch (data: E+1 into the neighbour's flag; ack: E into its ack word).
+//
+// Ring warps release at GPU scope (fence + relaxed atomic on the counter); the last arriver's atomic
+// observes them.  A system-scope fence costs microseconds on an idle machine and ~100 us while PCIe
+// copies are in flight (it also waits for the host side), and a pass cannot end before its slowest
+// thread: with the fence inside the pass, 8 GPUs lost 4-6 ms per 1000 iterations end to end
+// (profiles/e2e_probe.md).  So with peers on other devices the last arriver only stores the epoch
+// into a local word (release, GPU scope); a one-warp courier kernel on a side stream acquires it,
+// executes fence.sc.sys — cumulative over everything that happened before in causality order, i.e.
+// every ring warp's stores — and release-stores the flag into the neighbour.  Without a courier
+// (peers on this device, one-shot paths) the last arriver publishes itself.
 __device__ __forceinline__ void halo_publish(const HaloParams &h, const unsigned dmask, const uint32_t E,
                                              const int lane, const bool data) {
     __syncwarp();
     const bool mine = lane < 8 && ((dmask >> lane) & 1u) && h.peer_flag[lane] != nullptr;
     if (mine) {
         const long long t0 = h.prof ? clock64() : 0;
-        __threadfence_system();   // one fence per warp instruction; the barrier above makes it cover all lanes
+        __threadfence();   // one fence per warp instruction; the barrier above makes it cover all lanes
         const unsigned old = atomicAdd(h.counters + lane * 32, 1u);
         if ((int)old + 1 == h.expected[lane]) {
             h.counters[lane * 32] = 0;
-            __threadfence_system();
-            if (data) st_release_sys(h.peer_flag[lane], E + 1u);
-            else st_release_sys(h.peer_ack[lane], E);
+            uint32_t *const f = data ? h.peer_flag[lane] : h.peer_ack[lane];
+            const uint32_t v = data ? E + 1u : E;
+            if (h.ready) {
+                // hand the epoch to the courier: no system-scope fence inside a pass
+                asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(h.ready + ((data ? 0 : 8) + lane) * 32), "r"(v) : "memory");
+            } else if (h.flag_fence == 2) {
+                __threadfence();
+                asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(f), "r"(v) : "memory");
+            } else {
+                // the release store's own fence is also the acquire side of the counter atomic above
+                if (h.flag_fence == 0) __threadfence_system();
+                st_release_sys(f, v);
+            }
         }
         if (h.prof) {
             atomicAdd(h.prof + 17, (unsigned long long)(clock64() - t0));
@@ -529,13 +556,12 @@ __device__ __forceinline__ void halo_publish(const HaloParams &h, const unsigned
     }
 }
 
-// Whole per-warp program shared by the LDG and TMA kernels: pick the work item, wait for the
-// neighbours' epoch if this warp touches a halo frame, stream the band, publish our epoch.
+// One work item (band, chunk) of a pass: wait for the neighbours' epoch if this warp touches a
+// halo frame, stream the band, publish our epoch.  Shared by the per-pass kernels (LDG and TMA
+// feeds) and the persistent kernel.
 template <int K, int NW, int CH, bool CHECK, class MakeFeed>
-__device__ __forceinline__ void stream_warp(const PassParams &p, const int wid, const int lane, MakeFeed make_feed) {
-    int band, chunk;
-    map_work(wid, p.nbands, p.nchunks, p.halo.nbw, p.halo.nbe, band, chunk);
-
+__device__ __forceinline__ void stream_tile(const PassParams &p, const int band, const int chunk, const int lane,
+                                            MakeFeed make_feed) {
     constexpr int SB = NW * 4;
     const int x0 = band * p.vw - p.hlo;
     const int in_r0 = chunk * p.chunk_rows - K;
@@ -543,14 +569,6 @@ __device__ __forceinline__ void stream_warp(const PassParams &p, const int wid, 
     const bool edge = (p.zero_w && x0 < 0) || (p.zero_e && x0 + 32 * SB > p.bw) ||
                       (p.zero_n && in_r0 < 0) || (p.zero_s && in_r1 > p.rows);
     const bool partial = (p.bw % SB) != 0 && (band + 1) * p.vw >= p.bw;  // owns the cut last strip
-
-    // Programmatic dependent launch: everything above ran while the previous pass was still
-    // draining.  Let the pass after this one start scheduling, then wait until the previous
-    // pass (which wrote our source buffer) has completed and flushed.  Both are no-ops for
-    // launches without the programmatic-serialization attribute.
-    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-    asm volatile("griddepcontrol.wait;" ::: "memory");
-    if (p.converged && *p.converged) return;  // fixed point already reached: nothing changes any more
 
     bool top = false, bot = false, west = false, east = false;
     unsigned dmask = 0;   // directions whose ring this warp belongs to (bit = B2C_N .. B2C_SE)
@@ -578,6 +596,22 @@ __device__ __forceinline__ void stream_warp(const PassParams &p, const int wid, 
     if (dmask != 0 && (do_push || (h.mode & kHaloPostAck))) halo_publish(h, dmask, E, lane, do_push);
 }
 
+// Per-pass kernels: one warp = one work item of the pass.
+template <int K, int NW, int CH, bool CHECK, class MakeFeed>
+__device__ __forceinline__ void stream_warp(const PassParams &p, const int wid, const int lane, MakeFeed make_feed) {
+    int band, chunk;
+    map_work(wid, p.nbands, p.nchunks, p.raster ? p.nbands : p.halo.nbw, p.halo.nbe, band, chunk);
+
+    // Programmatic dependent launch: everything above ran while the previous pass was still
+    // draining.  Let the pass after this one start scheduling, then wait until the previous
+    // pass (which wrote our source buffer) has completed and flushed.  Both are no-ops for
+    // launches without the programmatic-serialization attribute.
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    if (p.converged && *p.converged) return;  // fixed point already reached: nothing changes any more
+    stream_tile<K, NW, CH, CHECK>(p, band, chunk, lane, make_feed);
+}
+
 template <int K, int NW, int CH, bool CHECK>
 __global__ void __launch_bounds__(kWarpsPerCta * 32, B2C_MIN_CTAS)
 stream_kernel(const PassParams p) {
@@ -585,6 +619,135 @@ stream_kernel(const PassParams p) {
     const int wid = blockIdx.x * kWarpsPerCta + (threadIdx.x >> 5);
     if (wid >= p.nbands * p.nchunks) return;
     stream_warp<K, NW, CH, CHECK>(p, wid, lane, [&]() { return LdgFeed<NW>(p, lane); });
+}
+
+// ---------------------------------------------------------------------------------------------
+// Persistent dataflow kernel: ONE launch runs every pass of a run.
+//
+// The per-pass kernels above meet at a grid-wide barrier after every K iterations (the kernel
+// boundary): a pass of 2.25 waves of warps costs three rounds, its slowest warp holds everybody
+// back, and every pass is a launch the front end has to fetch (measurably late when PCIe is busy
+// with the next image's upload).  None of that is needed: a work item (pass t, band b, chunk c)
+// depends only on the nine items (t-1, b+-1, c+-1) — they wrote what it reads, and they read what
+// it overwrites.  So resident warps pull items from one global counter, in pass order, and wait
+// on per-tile "passes completed" words instead of on the whole grid.  An item's dependencies are
+// always earlier in the queue, i.e. already taken by a warp that is running, so the scheme cannot
+// deadlock however many CTAs are resident (no cooperative launch needed).
+//
+// Replaces the host loop of cuda/cuda_convolution.cu:66-87 and mpi/mpi_convolution.c:156-240.
+struct PersistParams {
+    const PassParams *passes;      // [npasses], device memory
+    const int *cum;                // [npasses + 1] work items before pass t
+    int npasses;
+    unsigned long long *counter;   // global work counter (never reset; item_base = its value at launch)
+    unsigned long long item_base;
+    uint32_t *tile_done;           // [chunk * tstride + band]: passes completed by that tile, + pass_base
+    int tstride;
+    uint32_t pass_base;            // tile of pass t stores pass_base + t + 1
+    uint32_t epoch0;               // added to every pass's halo epoch (the exchange count at launch)
+    unsigned long long *prof;      // opt-in: [0] cycles waiting for tiles, [1] cycles in tiles, [2] total, [3] items, [4] waits
+};
+
+__device__ __forceinline__ uint32_t ld_acquire_gpu(const uint32_t *p) {
+    uint32_t v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ uint32_t ld_relaxed_gpu(const uint32_t *p) {
+    uint32_t v;
+    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_gpu(uint32_t *p, uint32_t v) {
+    asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+template <int K, int NW, int CH>
+__global__ void __launch_bounds__(kWarpsPerCta * 32, B2C_MIN_CTAS)
+stream_persist_kernel(const PersistParams q) {
+    static_assert(sizeof(PassParams) % 16 == 0, "PassParams is copied in 16-byte pieces");
+    __shared__ __align__(16) PassParams sp[kWarpsPerCta];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const PassParams &p = sp[warp];
+    const unsigned long long total = (unsigned long long)__ldg(q.cum + q.npasses);
+    int t = -1;                                   // pass whose parameters sit in sp[warp]
+    unsigned long long lo = 0, hi = 0;            // its item range [lo, hi)
+    int prev_nb = 1, prev_nc = 1;
+    // The next item is fetched before the current one is worked on, so the atomic's round trip hides
+    // behind a whole tile.  Still deadlock-free: a held item's dependencies are earlier in the queue,
+    // taken by running warps (possibly this one, which finishes its current tile first).
+    unsigned long long g = 0;
+    if (lane == 0) g = atomicAdd(q.counter, 1ull) - q.item_base;
+    g = __shfl_sync(kFull, g, 0);
+    long long c_wait = 0, c_tile = 0, n_items = 0, n_waits = 0;
+    const long long c_begin = q.prof ? clock64() : 0;
+    while (g < total) {
+        unsigned long long gnext = 0;
+        if (lane == 0) gnext = atomicAdd(q.counter, 1ull) - q.item_base;
+        if (g >= hi) {   // items only move forward: step to the pass that holds g (usually the next one)
+            do {
+                ++t;
+                lo = hi;
+                hi = (unsigned long long)__ldg(q.cum + t + 1);
+            } while (g >= hi);
+            if (t > 0) {   // tiling of the pass before (its extension may differ by one band / chunk)
+                prev_nb = __ldg(&q.passes[t - 1].nbands);
+                prev_nc = __ldg(&q.passes[t - 1].nchunks);
+            }
+            __syncwarp();
+            const uint4 *src = reinterpret_cast<const uint4 *>(q.passes + t);
+            uint4 *dst = reinterpret_cast<uint4 *>(&sp[warp]);
+            for (int i = lane; i < (int)(sizeof(PassParams) / 16); i += 32) dst[i] = __ldg(src + i);
+            __syncwarp();
+            if (lane == 0) sp[warp].halo.epoch += q.epoch0;
+            __syncwarp();
+        }
+        int band, chunk;
+        map_work((int)(g - lo), p.nbands, p.nchunks, p.raster ? p.nbands : p.halo.nbw, p.halo.nbe, band, chunk);
+        const long long c0 = q.prof ? clock64() : 0;
+        if (t > 0) {
+            // lanes 0-8: the 3x3 neighbourhood in the previous pass's tiling
+            if (lane < 9) {
+                int pb = band + lane % 3 - 1, pc = chunk + lane / 3 - 1;
+                pb = pb < 0 ? 0 : (pb >= prev_nb ? prev_nb - 1 : pb);
+                pc = pc < 0 ? 0 : (pc >= prev_nc ? prev_nc - 1 : pc);
+                const uint32_t *f = q.tile_done + (long long)pc * q.tstride + pb;
+                const uint32_t need = q.pass_base + (uint32_t)t;
+                if ((int)(ld_acquire_gpu(f) - need) < 0) {   // usually done long ago: one round trip
+                    const long long t0 = clock64();
+                    ++n_waits;
+                    do {
+                        __nanosleep(64);
+                        if (clock64() - t0 > (8ll << 30)) {
+                            printf("b200conv: tile dependency timeout pass=%d band=%d chunk=%d waits for (%d,%d)\n", t,
+                                   band, chunk, pb, pc);
+                            __trap();
+                        }
+                    } while ((int)(ld_acquire_gpu(f) - need) < 0);
+                }
+            }
+            __syncwarp();
+        }
+        const long long c1 = q.prof ? clock64() : 0;
+        stream_tile<K, NW, CH, false>(p, band, chunk, lane, [&]() { return LdgFeed<NW>(p, lane); });
+        __syncwarp();
+        if (lane == 0) st_release_gpu(q.tile_done + (long long)chunk * q.tstride + band, q.pass_base + (uint32_t)t + 1u);
+        if (q.prof) {
+            const long long c2 = clock64();
+            c_wait += c1 - c0;
+            c_tile += c2 - c1;
+            ++n_items;
+        }
+        g = __shfl_sync(kFull, gnext, 0);
+    }
+    if (q.prof && lane == 0) {
+        atomicAdd(q.prof + 0, (unsigned long long)c_wait);
+        atomicAdd(q.prof + 1, (unsigned long long)c_tile);
+        atomicAdd(q.prof + 2, (unsigned long long)(clock64() - c_begin));
+        atomicAdd(q.prof + 3, (unsigned long long)n_items);
+        n_waits = __reduce_add_sync(1u, (unsigned)n_waits);
+        atomicAdd(q.prof + 4, (unsigned long long)n_waits);
+    }
 }
 
 }  // namespace b2c

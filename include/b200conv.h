@@ -200,6 +200,9 @@ typedef struct b2c_opts {
                          naive kernel and cuda-compat, which have no change detector) */
     int halo_depth;   /* multi-rank: iterations between two halo exchanges = depth of the halo a
                          rank keeps (a multiple of tb, at most 32); 0 = auto */
+    int persistent;   /* run every pass of b2c_engine_run in ONE persistent kernel whose warps pull
+                         (pass, band, chunk) items from a queue and wait on per-tile flags instead of
+                         on kernel boundaries: -1 auto (on where it applies), 0 off, 1 on */
 } b2c_opts;
 
 void b2c_default_opts(b2c_opts *o);
@@ -273,6 +276,10 @@ int64_t b2c_engine_barrier_wait_cycles(b2c_engine *e);
  * epoch, [16] number of waits, [17] cycles spent in fence + count-in + publish, [18] number of
  * those, [24..31] / [32..39] longest single data / ack wait per direction. */
 int b2c_engine_set_profile(b2c_engine *e, int on);
+/* With B200CONV_PERSIST_PROF=1 in the environment: SM cycles summed over the persistent kernel's
+ * warps since the last call {waiting for tile dependencies, inside tiles, total, items, items
+ * that had to wait}.  Synchronises. */
+int b2c_engine_persist_profile(b2c_engine *e, uint64_t out[5]);
 int b2c_engine_halo_profile(b2c_engine *e, uint64_t out[40], int reset);
 
 /* Iterations actually executed by the last run (differs from `repetitions`

@@ -31,7 +31,7 @@ DIRS = ("N", "S", "W", "E", "NW", "NE", "SW", "SE")
 class Opts(C.Structure):
     _fields_ = [(n, C.c_int) for n in
                 ("boundary", "filter", "kernel", "tb", "strip_bytes", "chunk_rows", "use_graph", "check_every",
-                 "halo_depth")]
+                 "halo_depth", "persistent")]
 
 
 class EmulOpts(C.Structure):
@@ -104,6 +104,7 @@ def _load() -> C.CDLL:
         "b2c_engine_barrier_wait_cycles": (L, [P]),
         "b2c_engine_set_profile": (I, [P, I]),
         "b2c_engine_halo_profile": (I, [P, C.POINTER(C.c_uint64 * 40), I]),
+        "b2c_engine_persist_profile": (I, [P, C.POINTER(C.c_uint64 * 5)]),
         "b2c_debug_pass_plans": (I, [I, I, I, I, I, I, I, I, I, I, C.POINTER(I), I]),
         "b2c_engine_launches": (L, [P]),
         "b2c_resident_plan": (I, [I, I, I, I, I, C.POINTER(I)]),
@@ -137,7 +138,7 @@ def check(rc: int, what: str = "b200conv") -> int:
 
 
 def make_opts(boundary="zero", filter="gaussian", kernel="auto", tb=0, strip_bytes=0, chunk_rows=0,
-              use_graph=-1, check_every=0, halo_depth=0) -> Opts:
+              use_graph=-1, check_every=0, halo_depth=0, persistent=-1) -> Opts:
     o = Opts()
     lib.b2c_default_opts(C.byref(o))
     o.boundary = BOUNDARY[boundary] if isinstance(boundary, str) else int(boundary)
@@ -145,4 +146,5 @@ def make_opts(boundary="zero", filter="gaussian", kernel="auto", tb=0, strip_byt
     o.kernel = KERNEL[kernel] if isinstance(kernel, str) else int(kernel)
     o.tb, o.strip_bytes, o.chunk_rows = int(tb), int(strip_bytes), int(chunk_rows)
     o.use_graph, o.check_every, o.halo_depth = int(use_graph), int(check_every), int(halo_depth)
+    o.persistent = int(persistent)
     return o

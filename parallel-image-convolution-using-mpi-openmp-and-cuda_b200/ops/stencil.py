@@ -162,6 +162,12 @@ class Engine:
     def set_profile(self, on: bool = True):
         check(lib.b2c_engine_set_profile(self._h, int(bool(on))), "engine_set_profile")
 
+    def persist_profile(self) -> dict:
+        """B200CONV_PERSIST_PROF=1: where the persistent kernel's warps spent their cycles."""
+        buf = (C.c_uint64 * 5)()
+        check(lib.b2c_engine_persist_profile(self._h, C.byref(buf)), "engine_persist_profile")
+        return dict(zip(("wait_cycles", "tile_cycles", "total_cycles", "items", "waited_items"), list(buf)))
+
     def halo_profile(self, reset: bool = True) -> dict:
         """Wait-time counters of the halo protocol (SM cycles, summed over ring warps)."""
         from .._lib import DIRS

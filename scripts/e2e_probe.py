@@ -43,8 +43,13 @@ def main():
 
     # device-timed loop on resident data, for reference
     sh.load(dev_in)
+    sh.engine.set_profile(True)
     sh.timed_run(a.reps)
     loop_ms = sh.timed_run(a.reps)
+    hp = sh.engine.halo_profile(reset=True)
+    if rank == 0:
+        print("device-timed loop: avg publish cycles", hp["publish_cycles"] // max(1, hp["publishes"]), "avg wait",
+              (sum(hp["data_wait_cycles"].values()) + sum(hp["ack_wait_cycles"].values())) // max(1, hp["waits"]))
     rows = []
     for name, src, dsts in (("h2d+d2h", host_in, host_out), ("no copies", dev_in, dev_out),
                             ("h2d only", host_in, dev_out), ("d2h only", dev_in, host_out)):
@@ -58,12 +63,16 @@ def main():
         run = sum(t["run_end"] - t["run_start"] for t in tl[2:]) / (len(tl) - 2)
         h2d = sum(t["h2d_end"] - t["h2d_start"] for t in tl[2:]) / (len(tl) - 2)
         prep = sum(t["run_start"] - t["compute_free"] for t in tl[2:]) / (len(tl) - 2)
-        rows.append((name, mx(steady), mx(run), mx(h2d), mx(prep)))
+        hp = sh.engine.halo_profile(reset=True)
+        dw = sum(hp["data_wait_cycles"].values()) + sum(hp["ack_wait_cycles"].values())
+        rows.append((name, mx(steady), mx(run), mx(h2d), mx(prep), mx(dw / max(1, hp["waits"])),
+                     mx(hp["publish_cycles"] / max(1, hp["publishes"])), mx(max(hp["data_wait_max"].values()))))
     if rank == 0:
         print(f"{world} GPUs, {a.width}x{a.height} {a.color}, {a.reps} reps; device-timed loop {loop_ms:.3f} ms; plan {sh.engine.describe()}")
-        print(f"{'variant':12s} {'ms/image':>9s} {'loop':>8s} {'input copy':>11s} {'load+exch':>10s}")
+        print(f"{'variant':12s} {'ms/image':>9s} {'loop':>8s} {'input copy':>11s} {'load+exch':>10s} {'avg wait cyc':>13s} "
+              f"{'avg publish cyc':>16s} {'max data wait':>14s}")
         for r in rows:
-            print(f"{r[0]:12s} {r[1]:9.3f} {r[2]:8.3f} {r[3]:11.3f} {r[4]:10.3f}", flush=True)
+            print(f"{r[0]:12s} {r[1]:9.3f} {r[2]:8.3f} {r[3]:11.3f} {r[4]:10.3f} {r[5]:13.0f} {r[6]:16.0f} {r[7]:14.0f}", flush=True)
     sh.close()
     dist.destroy_process_group()
 

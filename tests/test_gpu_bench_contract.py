@@ -21,7 +21,7 @@ def test_bench_json_contract():
               "vs_baseline", "dtype", "data", "config", "clocks", "e2e", "gpu_launches"):
         assert k in d, k
     assert d["n_gpus"] == 1 and d["steps"] == 2 and d["warmup"] == 3 and d["higher_is_better"] is True
-    assert d["value"] > 0 and d["gpu_launches"] == 2 * 4          # 16 reps = 4 passes of K=4 per step
+    assert d["value"] > 0 and 2 <= d["gpu_launches"] <= 2 * 4     # per step: one persistent kernel, or 4 passes of K=4
     assert d["e2e"]["value"] > 0 and d["e2e"]["h2d_bytes_per_step"] == 2048 * 2048 * 3
     # (for images this small the pipelined end-to-end rate may exceed the single-stream device
     #  rate: two engines on two streams fill a GPU that one latency-bound image cannot)

@@ -174,3 +174,33 @@ def test_run_inside_a_callers_stream_capture():
     torch.cuda.synchronize()
     assert (out.cpu().numpy() == reference_oracle(img, 40, "zero")).all()
     eng.close()
+
+
+@pytest.mark.parametrize("boundary", ["zero", "torus"])
+@pytest.mark.parametrize("ch", [1, 3])
+def test_persistent_kernel_and_per_pass_launches_agree(boundary, ch):
+    """One persistent kernel with per-tile dependencies (the default) against one launch per pass."""
+    img = rnd(700, 2100, ch, seed=77)
+    for reps, opts in ((43, dict(tb=4)), (30, dict(tb=4, chunk_rows=16)), (17, dict(tb=8, strip_bytes=8)),
+                       (64, dict(tb=4, halo_depth=16, chunk_rows=24))):
+        want = reference_oracle(img, reps, boundary)
+        for persistent in (1, 0):
+            got = gpu_blur(img, reps, boundary=boundary, kernel="stream", persistent=persistent, **opts)
+            assert (got == want).all(), f"persistent={persistent} {opts}: {np.argwhere(got != want)[:4]}"
+
+
+def test_persistent_kernel_is_one_launch_per_run():
+    img = rnd(512, 1024, 3, seed=78)
+    eng = b200conv.Engine(1024, 512, 3, tb=4, persistent=1)
+    eng.load(torch.from_numpy(img).cuda())
+    eng.exchange()
+    l0 = eng.launches
+    eng.run(400)
+    assert eng.launches - l0 == 1
+    eng.run(400)
+    eng.run(203)   # 50 passes in the table + k=2 and k=1 launched on their own
+    out = torch.empty(img.shape, dtype=torch.uint8, device="cuda")
+    eng.store(out)
+    torch.cuda.synchronize()
+    assert (out.cpu().numpy() == reference_oracle(img, 1003, "zero")).all()
+    eng.close()
