@@ -81,6 +81,10 @@ def run_b200conv(a):
         if world == 1 and a.gpus > 1:
             raise SystemExit("launch with torch.distributed.run --nproc-per-node N for --gpus N")
         a.gpus = world
+    numa_cpus = None
+    if world > 1 and os.environ.get("B200CONV_NUMA_BIND", "1") != "0":
+        from b200conv.utils.affinity import bind_to_gpu_numa
+        numa_cpus = bind_to_gpu_numa(local)   # pinned staging buffers on the GPU's own NUMA node
     torch.cuda.set_device(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
@@ -314,6 +318,8 @@ def run_b200conv(a):
             "clocks": sampler.summary() if sampler else None,
             "e2e": e2e,
         }
+        if numa_cpus:
+            out["config"]["host_numa_binding"] = f"rank 0 bound to {len(numa_cpus)} CPUs local to its GPU"
         if eng is not None and getattr(eng, "tuned", None):
             out["config"]["coupled_tuning"] = eng.tuned
         if start_wait is not None:

@@ -91,6 +91,7 @@ struct PersistPlan {
     int tstride = 0;
     long long tile_words = 0;
     uint32_t groups = 0;              // exchanges completed by the table's passes
+    CourierParams *d_courier = nullptr;  // the kernel's own courier (null: the last arrivers publish themselves)
     std::vector<Pass> all;            // the whole run
 };
 
@@ -180,6 +181,7 @@ void drop_graphs(b2c_engine *e) {
             cudaFree(kv.second.d_passes);
             cudaFree(kv.second.d_cum);
             cudaFree(kv.second.d_counters);
+            cudaFree(kv.second.d_courier);
         }
         e->persist.clear();
     }
@@ -551,7 +553,10 @@ int persist_plan(b2c_engine *e, int reps, PersistPlan **out) {
         const uint32_t epoch0 = e->epoch, dev0 = e->epoch_dev;
         e->epoch_dev = e->epoch;
         const bool courier0 = e->courier_on;
-        e->courier_on = want_courier(e);
+        bool publishes = false;   // does any pass of the table publish an epoch?
+        for (size_t t = 0; t < np; ++t) publishes |= (pl.all[t].mode & (kHaloPush | kHaloPostAck)) != 0;
+        const bool courier = want_courier(e) && publishes;
+        e->courier_on = courier;
         int max_nb = 1, max_nc = 1;
         for (size_t t = 0; t < np; ++t) {
             const Pass &ps = pl.all[t];
@@ -577,6 +582,24 @@ int persist_plan(b2c_engine *e, int reps, PersistPlan **out) {
         CK(cudaMalloc(&pl.d_cum, (np + 1) * sizeof(int)));
         CK(cudaMemcpy(pl.d_passes, tab.data(), np * sizeof(PassParams), cudaMemcpyHostToDevice));
         CK(cudaMemcpy(pl.d_cum, cum.data(), (np + 1) * sizeof(int), cudaMemcpyHostToDevice));
+        if (courier) {
+            CourierParams c{};
+            c.ready = e->pad + kPadReady;
+            for (int d = 0; d < 8; ++d) {
+                if (e->nb[d] < 0) continue;
+                c.peer_flag[d] = e->peer_pad[d] + kPadFlags + opposite_dir(d) * 32;
+                c.peer_ack[d] = e->peer_pad[d] + kPadAcks + opposite_dir(d) * 32;
+            }
+            uint32_t g = 0;
+            for (size_t t = 0; t < np; ++t) {
+                if (pl.all[t].mode & kHaloPostAck) { c.has_ack = 1; c.final_ack = g; }
+                if (pl.all[t].group_end) g++;
+            }
+            c.start_epoch = 0;          // the kernel adds the epoch at launch
+            c.final_data = pl.groups;
+            CK(cudaMalloc(&pl.d_courier, sizeof c));
+            CK(cudaMemcpy(pl.d_courier, &c, sizeof c, cudaMemcpyHostToDevice));
+        }
     }
     *out = &e->persist.emplace(key, std::move(pl)).first->second;
     return B2C_OK;
@@ -612,11 +635,9 @@ int run_persistent(b2c_engine *e, int reps, cudaStream_t s) {
             e->persist_ctas = occ * e->sm_count;
         }
     }
-    // every allocation (and the synchronisation that may come with it) is behind us: the courier
-    // waits for epochs that only the launches below produce
-    if ((rc = courier_begin(e, pl->all, false, s)) != B2C_OK) return rc;
     if (pl->npasses > 0) {
         PersistParams q{};
+        q.courier = pl->d_courier;
         q.passes = pl->d_passes;
         q.cum = pl->d_cum;
         q.npasses = pl->npasses;
@@ -639,8 +660,7 @@ int run_persistent(b2c_engine *e, int reps, cudaStream_t s) {
         e->epoch += pl->groups;
     }
     for (size_t t = (size_t)pl->npasses; t < pl->all.size(); ++t)   // k < K at the end of the run
-        if ((rc = enqueue_pass(e, pl->all[t], false, s)) != B2C_OK) return rc;
-    if ((rc = courier_end(e, s)) != B2C_OK) return rc;
+        if ((rc = enqueue_pass(e, pl->all[t], false, s)) != B2C_OK) return rc;   // these publish their epochs themselves
     return enqueue_epoch_sync(e, false, s);
 }
 
@@ -1221,7 +1241,7 @@ namespace {
 // The iteration loop of the streaming kernels: one persistent kernel, or one launch per pass
 // (replayed as a CUDA graph when the run is long enough).
 int run_streaming(b2c_engine *e, int reps, cudaStream_t s) {
-    if (persist_enabled(e) && !(want_courier(e) && !s)) {   // the courier cannot run beside the legacy default stream
+    if (persist_enabled(e)) {
         e->iters_done = reps;
         return run_persistent(e, reps, s);
     }

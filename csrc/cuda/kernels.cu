@@ -371,33 +371,7 @@ __global__ void barrier_kernel(const BarrierParams b) {
     if (lane == 0 && b.skew_cycles) *b.skew_cycles = (unsigned long long)(clock64() - t0);
 }
 
-__global__ void courier_kernel(const CourierParams c) {
-    const int lane = threadIdx.x;
-    const int d = lane & 7;
-    const bool ack = lane >= 8;
-    uint32_t *const dst = ack ? c.peer_ack[d] : c.peer_flag[d];
-    if (lane >= 16 || !dst || (ack && !c.has_ack)) return;
-    const uint32_t base = c.epoch_base ? __ldcg(c.epoch_base) : 0u;
-    const uint32_t last = base + (ack ? c.final_ack : c.final_data);
-    uint32_t sent = base + c.start_epoch - (ack ? 1u : 0u);   // acks carry the epoch of their own group
-    const uint32_t *const src = c.ready + lane * 32;
-    long long t0 = clock64();
-    while ((int)(sent - last) < 0) {
-        const uint32_t v = ld_acquire_gpu(src);
-        if ((int)(v - sent) > 0 && (int)(v - last) <= 0) {
-            __threadfence_system();    // fence.sc.sys: cumulative over the ring warps' stores
-            st_release_sys(dst, v);
-            sent = v;
-            t0 = clock64();
-        } else {
-            __nanosleep(200);
-            if (clock64() - t0 > (40ll << 30)) {
-                printf("b200conv: courier timeout dir=%d %s sent=%u last=%u ready=%u\n", d, ack ? "ack" : "data", sent, last, v);
-                __trap();
-            }
-        }
-    }
-}
+__global__ void courier_kernel(const CourierParams c) { courier_loop(c, threadIdx.x, 0u); }
 
 cudaError_t launch_courier(const CourierParams &c, cudaStream_t s) {
     courier_kernel<<<1, 32, 0, s>>>(c);

@@ -72,19 +72,7 @@ struct BarrierParams {
 };
 cudaError_t launch_barrier(const BarrierParams &b, cudaStream_t s);
 
-// Courier: one warp that lives beside a run and forwards halo epochs from local "ready" words to
-// the neighbours' flag / ack words with system-scope ordering (lane d: data flag of direction d,
-// lane 8+d: ack of direction d).  It leaves when the last epoch of the run has been forwarded.
-struct CourierParams {
-    const uint32_t *ready;        // [16][32] words
-    uint32_t *peer_flag[8];
-    uint32_t *peer_ack[8];
-    const uint32_t *epoch_base;   // added to the three values below (null: 0)
-    uint32_t start_epoch;         // data epochs up to this one are already published
-    uint32_t final_data;          // last data epoch of the run
-    uint32_t final_ack;           // last ack epoch of the run
-    int has_ack;                  // 0: no group of the run acknowledges
-};
+struct CourierParams;   // stencil_stream.cuh
 cudaError_t launch_courier(const CourierParams &c, cudaStream_t s);
 
 long long total_launches();

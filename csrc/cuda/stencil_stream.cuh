@@ -621,6 +621,56 @@ stream_kernel(const PassParams p) {
     stream_warp<K, NW, CH, CHECK>(p, wid, lane, [&]() { return LdgFeed<NW>(p, lane); });
 }
 
+// Courier: one warp that lives beside a run and forwards halo epochs from local "ready" words to
+// the neighbours' flag / ack words with system-scope ordering (lane d: data flag of direction d,
+// lane 8+d: ack of direction d).  It leaves when the last epoch of the run has been forwarded.
+// Runs as a one-warp kernel on a side stream beside per-pass launches (kernels.cu), and as warp 0
+// of CTA 0 inside the persistent kernel — whose CTAs fill every SM, so that a separate kernel
+// might never become resident.
+struct CourierParams {
+    const uint32_t *ready;        // [16][32] words
+    uint32_t *peer_flag[8];
+    uint32_t *peer_ack[8];
+    const uint32_t *epoch_base;   // added to the three values below (null: 0)
+    uint32_t start_epoch;         // data epochs up to this one are already published
+    uint32_t final_data;          // last data epoch of the run
+    uint32_t final_ack;           // last ack epoch of the run
+    int has_ack;                  // 0: no group of the run acknowledges
+};
+
+__device__ __forceinline__ uint32_t ld_acquire_gpu(const uint32_t *p) {
+    uint32_t v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+__device__ __forceinline__ void courier_loop(const CourierParams &c, const int lane, const uint32_t add) {
+    const int d = lane & 7;
+    const bool ack = lane >= 8;
+    uint32_t *const dst = ack ? c.peer_ack[d] : c.peer_flag[d];
+    if (lane >= 16 || !dst || (ack && !c.has_ack)) return;
+    const uint32_t base = add + (c.epoch_base ? __ldcg(c.epoch_base) : 0u);
+    const uint32_t last = base + (ack ? c.final_ack : c.final_data);
+    uint32_t sent = base + c.start_epoch - (ack ? 1u : 0u);   // acks carry the epoch of their own group
+    const uint32_t *const src = c.ready + lane * 32;
+    long long t0 = clock64();
+    while ((int)(sent - last) < 0) {
+        const uint32_t v = ld_acquire_gpu(src);
+        if ((int)(v - sent) > 0 && (int)(v - last) <= 0) {
+            __threadfence_system();    // fence.sc.sys: cumulative over the ring warps' stores
+            st_release_sys(dst, v);
+            sent = v;
+            t0 = clock64();
+        } else {
+            __nanosleep(200);
+            if (clock64() - t0 > (40ll << 30)) {
+                printf("b200conv: courier timeout dir=%d %s sent=%u last=%u ready=%u\n", d, ack ? "ack" : "data", sent, last, v);
+                __trap();
+            }
+        }
+    }
+}
+
 // ---------------------------------------------------------------------------------------------
 // Persistent dataflow kernel: ONE launch runs every pass of a run.
 //
@@ -646,13 +696,9 @@ struct PersistParams {
     uint32_t pass_base;            // tile of pass t stores pass_base + t + 1
     uint32_t epoch0;               // added to every pass's halo epoch (the exchange count at launch)
     unsigned long long *prof;      // opt-in: [0] cycles waiting for tiles, [1] cycles in tiles, [2] total, [3] items, [4] waits
+    const CourierParams *courier;  // when set: warp 0 of CTA 0 is the courier (epochs relative to epoch0)
 };
 
-__device__ __forceinline__ uint32_t ld_acquire_gpu(const uint32_t *p) {
-    uint32_t v;
-    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
-}
 __device__ __forceinline__ uint32_t ld_relaxed_gpu(const uint32_t *p) {
     uint32_t v;
     asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
@@ -668,6 +714,10 @@ stream_persist_kernel(const PersistParams q) {
     static_assert(sizeof(PassParams) % 16 == 0, "PassParams is copied in 16-byte pieces");
     __shared__ __align__(16) PassParams sp[kWarpsPerCta];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (q.courier && blockIdx.x == 0 && warp == 0) {   // CTA 0 is resident from the first instant
+        courier_loop(*q.courier, lane, q.epoch0);
+        return;
+    }
     const PassParams &p = sp[warp];
     const unsigned long long total = (unsigned long long)__ldg(q.cum + q.npasses);
     int t = -1;                                   // pass whose parameters sit in sp[warp]

@@ -34,6 +34,10 @@ def main():
         (256, 512, 3, 203, "torus", dict(tb=4, halo_depth=8, delay=30000)),
         (256, 1024, 1, 330, "zero", dict(tb=4, halo_depth=16, delay=10000, twice=True)),
         (512, 1024, 3, 1000, "torus", dict(tb=4, halo_depth=32, use_graph=1, twice=True)),
+        # the persistent kernel with neighbours: its own courier warp, tail passes (203 = 25 groups of 8 + 2 + 1)
+        (512, 1024, 3, 300, "torus", dict(tb=4, halo_depth=16, persistent=1, twice=True)),
+        (256, 512, 3, 203, "zero", dict(tb=4, halo_depth=8, persistent=1, delay=20000)),
+        (256, 512, 1, 90, "torus", dict(tb=4, halo_depth=12, persistent=1)),    # groups 4+4+4, last group 4+2
         (240, 200, 3, 57, "torus", dict(tb=4, halo_depth=12)),      # unaligned width: push kernel after each group
         (512, 1024, 3, 90, "zero", dict(tb=4, halo_depth=16, kernel="tma")),
         (512, 512, 1, 800, "torus", dict(tb=4, halo_depth=16, check_every=20)),
