@@ -150,6 +150,7 @@ struct b2c_engine {
     long long res_xpitch = 0;
     uint32_t *res_flags = nullptr;   // sm_count x 32 words, then the error word
     uint32_t res_epoch = 0;
+    int res_cx = 0;                  // cluster width of the resident kernel (0: not asked yet)
     mutable std::map<std::pair<int, int>, BandPlan> plan_cache;   // key (k, ext)
     // persistent dataflow kernel: per (reps, cur) a device table of pass parameters
     std::map<std::pair<int, int>, PersistPlan> persist;
@@ -683,6 +684,16 @@ int enqueue_epoch_sync(b2c_engine *e, bool device_epoch, cudaStream_t s) {
 void choose_plan(b2c_engine *e) {
     const b2c_opts &o = e->opts;
     e->kernel = o.kernel == B2C_KERNEL_AUTO ? B2C_KERNEL_STREAM : o.kernel;
+    // AUTO: an image that fits the register files of the chip stays there for the whole run
+    // (stencil_resident.cu; 1920x2520 grey: 2.1x the streaming kernel).  Any option that only
+    // the streaming kernels understand keeps them.
+    static const bool res_auto = !(getenv("B200CONV_RESIDENT_AUTO") && atoi(getenv("B200CONV_RESIDENT_AUTO")) == 0);
+    if (res_auto && o.kernel == B2C_KERNEL_AUTO && o.filter == B2C_GAUSSIAN && e->P * e->Q == 1 &&
+        o.boundary != B2C_CUDA_COMPAT && o.check_every == 0 && o.strip_bytes == 0 && o.chunk_rows == 0 &&
+        o.halo_depth == 0 && o.persistent < 0 && o.use_graph < 0) {
+        for (int k = 16; k >= 4; k >>= 1)
+            if (resident_plan(e->bw, e->R, e->CH, k, e->sm_count, nullptr)) e->kernel = B2C_KERNEL_RESIDENT;
+    }
     if (o.filter != B2C_GAUSSIAN) e->kernel = B2C_KERNEL_NAIVE;
     int K = o.tb > 0 ? o.tb : 4;
     if (K >= 8) K = 8; else if (K >= 4) K = 4; else if (K >= 2) K = 2; else K = 1;
@@ -927,12 +938,16 @@ b2c_engine *b2c_engine_create(int device, int W, int H, int CH, int P, int Q, in
                 if (us_per_iteration < best) { best = us_per_iteration; e->res_plan = pl; fits = true; }
             }
         }
-        if (P * Q != 1 || o.boundary == B2C_CUDA_COMPAT || !coop || !fits) {
+        if ((P * Q != 1 || o.boundary == B2C_CUDA_COMPAT || !coop || !fits) && o.kernel == B2C_KERNEL_AUTO) {
+            e->kernel = B2C_KERNEL_STREAM;   // AUTO never fails on this: the streaming kernel takes anything
+        } else if (P * Q != 1 || o.boundary == B2C_CUDA_COMPAT || !coop || !fits) {
             set_error("the resident kernel needs one GPU, zero/torus, row bytes %% 8 == 0 and an image that fits "
                       "the register files (%d x %d bytes does not, or cooperative launch is missing)", e->bw, e->R);
             b2c_engine_destroy(e);
             return nullptr;
         }
+    }
+    if (e->kernel == B2C_KERNEL_RESIDENT) {
         e->res_xpitch = round_up(e->bw, 128);
         const size_t xbytes = (size_t)(e->res_xpitch * e->R), fbytes = ((size_t)e->sm_count * 32 + 32) * sizeof(uint32_t);
         if (cudaMalloc(&e->res_xbuf[0], xbytes) != cudaSuccess || cudaMalloc(&e->res_xbuf[1], xbytes) != cudaSuccess ||
@@ -1221,6 +1236,8 @@ int b2c_engine_run(b2c_engine *e, int reps, void *stream) {
         q.strips = e->res_plan.strips;
         q.ctarows = e->res_plan.ctarows;
         q.torus = e->opts.boundary == B2C_TORUS;
+        if (!e->res_cx) e->res_cx = resident_cluster_width(e->res_plan, e->CH);
+        q.cx = e->res_cx;
         {
             const char *dbg = getenv("B200CONV_RES_DEBUG");   // profiling only, see stencil_resident.cu
             q.debug = dbg ? atoi(dbg) : 0;
@@ -1402,9 +1419,9 @@ int b2c_engine_describe(const b2c_engine *e, char *buf, size_t buflen) {
         return B2C_OK;
     }
     if (e->kernel == B2C_KERNEL_RESIDENT) {
-        snprintf(buf, buflen, "kernel=resident tb=%d ctas=%dx%d rows_per_warp=%d valid=%dx%dB block=%dx%d(bytes %d)",
-                 e->res_plan.k, e->res_plan.ctarows, e->res_plan.strips, e->res_plan.rw, e->res_plan.vr, e->res_plan.vc, e->R, e->C,
-                 e->bw);
+        snprintf(buf, buflen, "kernel=resident tb=%d ctas=%dx%d cluster=%dx1 rows_per_warp=%d valid=%dx%dB block=%dx%d(bytes %d)",
+                 e->res_plan.k, e->res_plan.ctarows, e->res_plan.strips, e->res_cx > 0 ? e->res_cx : 1, e->res_plan.rw,
+                 e->res_plan.vr, e->res_plan.vc, e->R, e->C, e->bw);
         return B2C_OK;
     }
     const BandPlan bp = make_band_plan(e, e->K, 0);
@@ -1429,7 +1446,7 @@ int b2c_debug_band_plan(int rows, int cols, int channels, int has_neighbours, in
     e.opts.tb = tb;
     e.opts.strip_bytes = strip_bytes;
     e.opts.chunk_rows = chunk_rows;
-    e.opts.kernel = kernel;
+    e.opts.kernel = kernel == B2C_KERNEL_AUTO ? B2C_KERNEL_STREAM : kernel;   // the plan of the streaming kernels
     e.R = rows, e.C = cols, e.CH = channels, e.bw = cols * channels;
     e.W = cols, e.H = rows;
     e.any_nb = has_neighbours != 0;
@@ -1456,6 +1473,7 @@ int b2c_debug_pass_plans(int rows, int cols, int channels, int has_neighbours, i
     e.opts.strip_bytes = strip_bytes;
     e.opts.chunk_rows = chunk_rows;
     e.opts.halo_depth = halo_depth;
+    e.opts.kernel = B2C_KERNEL_STREAM;
     e.R = rows, e.C = cols, e.CH = channels, e.bw = cols * channels;
     e.W = cols, e.H = rows;
     e.any_nb = has_neighbours != 0;
@@ -1606,6 +1624,19 @@ int b2c_engine_set_delay(b2c_engine *e, int64_t cycles) {
 
 int b2c_blur_device(const uint8_t *d_in, int64_t in_pitch, uint8_t *d_out, int64_t out_pitch, int W, int H,
                     int CH, int reps, const b2c_opts *opts, void *stream) {
+    // argument errors keep their own codes; only what CUDA refuses is B2C_ECUDA
+    if (!d_in || !d_out || W <= 0 || H <= 0 || (CH != 1 && CH != 3) || reps < 0) {
+        set_error("blur_device: bad arguments W=%d H=%d CH=%d reps=%d", W, H, CH, reps);
+        return B2C_EINVAL;
+    }
+    if ((long long)W * CH > (1ll << 30)) {
+        set_error("blur_device: row too wide");
+        return B2C_ETOOBIG;
+    }
+    if (opts && opts->boundary == B2C_CUDA_COMPAT && opts->filter != B2C_GAUSSIAN) {
+        set_error("cuda-compat is gaussian only (like cuda/cuda_convolution.cu)");
+        return B2C_EINVAL;
+    }
     int dev = 0;
     CK(cudaGetDevice(&dev));
     b2c_engine *e = b2c_engine_create(dev, W, H, CH, 1, 1, 0, opts);
@@ -1654,8 +1685,10 @@ int64_t b2c_total_launches(void) { return total_launches(); }
 //
 // The scratch is shared by all calls and keeps whatever the previous call left in it, so
 // each call first clears the part it is going to use (halo frames and flag words must
-// start at zero).  Two calls whose GPU work overlaps — different streams, or different
-// host threads on different streams — corrupt each other; calls on one stream are safe.
+// start at zero).  Two calls whose GPU work overlaps — different streams — corrupt each other.
+// Enqueueing is serialised inside the function (a mutex around the memset / copy / pass
+// launches), so several host threads may call it on ONE stream; the calls then run one after
+// the other in the order the threads got the lock.
 // ---------------------------------------------------------------------------------------
 #define B2C_NOALLOC_SCRATCH_BYTES (32ll << 20)
 
@@ -1704,6 +1737,8 @@ extern "C" int b2c_blur_device_noalloc(const uint8_t *d_in, int64_t in_pitch, ui
     b2c_default_opts(&e.opts);
     e.opts.boundary = boundary;
     e.opts.use_graph = 0;
+    e.opts.kernel = B2C_KERNEL_STREAM;   // the kernels that need nothing but the two framed buffers and the pad
+    e.opts.persistent = 0;
     e.R = H; e.C = W; e.row0 = 0; e.col0 = 0;
     if ((long long)W * CH > (1ll << 30)) {
         set_error("blur_device_noalloc: row too wide");
@@ -1743,6 +1778,10 @@ extern "C" int b2c_blur_device_noalloc(const uint8_t *d_in, int64_t in_pitch, ui
     e.pad = reinterpret_cast<uint32_t *>(scratch + 2 * e.alloc_bytes);
     for (int i = 0; i < 2; ++i) e.base[i] = e.alloc[i] + (long long)kFrameRows * e.pitch + kLeftPad;
 
+    // One call's commands go into the stream as a block: two host threads interleaving their
+    // memset / copy / launches on the same stream would run each other's passes on half-cleared scratch.
+    static std::mutex enqueue_mu;
+    std::lock_guard<std::mutex> enqueue_lock(enqueue_mu);
     // The last call's image, halo frames, epoch flags and counters are still in there.
     CK(cudaMemsetAsync(scratch, 0, (size_t)need, s));
     if (e.any_nb) {  // torus on one GPU: the rank is its own neighbour in all eight directions

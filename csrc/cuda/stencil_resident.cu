@@ -21,6 +21,13 @@
 //     Same slot-reuse argument as the multi-GPU protocol: a CTA can write epoch e+2 only after it
 //     has seen its neighbours' epoch e+1, which they publish after reading epoch e.
 //     Measured: an iteration costs ~66 ns per row held by a warp, an exchange ~4 us.
+//   * thread-block clusters + distributed shared memory: the CTAs of one tile row are launched as
+//     clusters of up to 8 (p.cx, a divisor of the strip count).  West/east neighbours inside a
+//     cluster do not go through L2 for their halo columns: the owner stores its ring columns
+//     straight into the neighbour's shared-memory inbox (generic stores to a map_shared_rank
+//     address = st.shared::cluster), one barrier.cluster (arrive.release / wait.acquire) replaces
+//     their flag handshake, and the halo comes back with LDS.  North/south and diagonal
+//     neighbours live in other clusters and keep the L2 path.
 //   * ZERO boundary: cells outside the image are forced to zero by the mask / byte-permute that
 //     does the >>4 anyway (no extra instruction); TORUS: halo loads wrap around the image.
 //
@@ -28,25 +35,22 @@
 // iteration from the host and re-reads the whole image from DRAM every time).
 #include "stencil_resident.h"
 
+#include <cooperative_groups.h>
 #include <cuda_runtime.h>
+
+#include <mutex>
 
 #include "common.h"
 #include "kernels.h"
 #include "stencil_stream.cuh"
+
+namespace cg = cooperative_groups;
 
 namespace b2c {
 namespace {
 
 constexpr long long kResTimeout = 3ll << 30;  // clocks (~1.6 s) before a wait gives up
 
-__device__ __forceinline__ uint32_t ld_acquire_gpu(const uint32_t *p) {
-    uint32_t v;
-    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ void st_release_gpu(uint32_t *p, uint32_t v) {
-    asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
 
 // 8 bytes at (gr, gc) of an H x bw byte image; outside the image: wrapped (torus) or zero.
 // gc and bw are multiples of 8, so a strip is never split by the image edge.
@@ -155,10 +159,22 @@ __global__ void __launch_bounds__(kResWarps * 32, 1) resident_kernel(const Resid
     constexpr int VR = kResWarps * RW - 2 * K;   // valid rows per CTA
     constexpr int VC = kResWinB - 2 * HB;        // valid bytes per CTA
     __shared__ ResShared sh;
+    // inbox[epoch parity][0 = from the west neighbour, 1 = from the east][row of the CTA][8-byte slot]
+    extern __shared__ __align__(16) uint2 inbox[];
+    constexpr int kSlots = HB / SB, kRows = kResWarps * RW;
+    cg::cluster_group cluster = cg::this_cluster();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int bx = blockIdx.x % p.strips, by = blockIdx.x / p.strips;
     const bool torus = p.torus != 0;
     if (threadIdx.x == 0) sh.abort = 0;   // ordered before its first read by the barriers in between
+    // West / east neighbour inside this cluster?  (clusters are cx consecutive strips of one tile row;
+    // the torus wrap-around pair is in the same cluster only when the cluster is the whole row)
+    const int cx = p.cx, crank = bx % (cx > 0 ? cx : 1);
+    const bool whole_row = cx == p.strips && cx > 1;
+    const bool w_in = cx > 1 && (crank > 0 || (torus && whole_row));
+    const bool e_in = cx > 1 && (crank + 1 < cx || (torus && whole_row));
+    uint2 *const w_peer = w_in ? cluster.map_shared_rank(inbox, (crank + cx - 1) % cx) : nullptr;   // its "from the east" side
+    uint2 *const e_peer = e_in ? cluster.map_shared_rank(inbox, (crank + 1) % cx) : nullptr;        // its "from the west" side
 
     // This CTA's valid region, this lane's strip, this warp's rows — all in image coordinates.
     const int vr0 = by * VR, vr1 = min(vr0 + VR, p.H);
@@ -209,13 +225,23 @@ __global__ void __launch_bounds__(kResWarps * 32, 1) resident_kernel(const Resid
         // ---- exchange: ring out, epoch, neighbours' epochs, halo in
         ++epoch;
         uint8_t *const xb = (epoch & 1u) ? p.xbuf[1] : p.xbuf[0];
+        const int par = (int)(epoch & 1u);
 #pragma unroll
         for (int r = 0; r < RW; ++r) {
             const int gr = wr0 + r;
             const bool row_valid = gr >= vr0 && gr < vr1;
             const bool row_ring = gr < vr0 + K || gr >= vr1 - K;
-            if (row_valid && col_valid && (row_ring || col_ring))
-                __stcg(reinterpret_cast<uint2 *>(xb + (long long)gr * p.xpitch + gc), res_pack(E[r], O[r]));
+            if (row_valid && col_valid) {
+                const bool ring_w = gc < vc0 + HB, ring_e = gc >= vc1 - HB;
+                const uint2 packed = res_pack(E[r], O[r]);
+                // ring columns go into the shared memory of a west / east neighbour of this cluster ...
+                const int lr = warp * RW + r;
+                if (ring_w && w_in) w_peer[((par * 2 + 1) * kRows + lr) * kSlots + (gc - vc0) / SB] = packed;
+                if (ring_e && e_in) e_peer[((par * 2 + 0) * kRows + lr) * kSlots + (gc - (vc1 - HB)) / SB] = packed;
+                // ... and into the exchange image in L2 for everybody else
+                if (row_ring || (ring_w && !w_in) || (ring_e && !e_in))
+                    __stcg(reinterpret_cast<uint2 *>(xb + (long long)gr * p.xpitch + gc), packed);
+            }
         }
         // barrier, then ONE gpu-scope fence by the thread that publishes (the grid-sync pattern of
         // cooperative groups): the barrier orders every thread's ring stores before thread 0's fence,
@@ -225,22 +251,25 @@ __global__ void __launch_bounds__(kResWarps * 32, 1) resident_kernel(const Resid
             __threadfence();
             st_release_gpu(p.flags + (long long)blockIdx.x * 32, epoch);
         }
+        // in-cluster neighbours: their ring sits in our inbox once everybody has passed this barrier
+        if (cx > 1) cluster.sync();
         if (threadIdx.x < 8) {
             int ny = by + kDirDrDev(threadIdx.x), nx = bx + kDirDcDev(threadIdx.x);
-            bool exists = true;
+            bool exists = !((threadIdx.x == B2C_W && w_in) || (threadIdx.x == B2C_E && e_in));
             if (torus) {
                 ny = ny < 0 ? ny + p.ctarows : (ny >= p.ctarows ? ny - p.ctarows : ny);
                 nx = nx < 0 ? nx + p.strips : (nx >= p.strips ? nx - p.strips : nx);
             } else {
-                exists = ny >= 0 && ny < p.ctarows && nx >= 0 && nx < p.strips;
+                exists = exists && ny >= 0 && ny < p.ctarows && nx >= 0 && nx < p.strips;
             }
             if (exists) {
                 const uint32_t *f = p.flags + (long long)(ny * p.strips + nx) * 32;
                 const long long t0 = clock64();
                 while ((int)(ld_acquire_gpu(f) - epoch) < 0) {
                     if (clock64() - t0 > kResTimeout) {
-                        sh.abort = 1;
                         atomicExch(p.error, 1u);
+                        if (cx > 1) __trap();   // cluster mates would wait for ever at their next barrier
+                        sh.abort = 1;
                         break;
                     }
                 }
@@ -265,8 +294,15 @@ __global__ void __launch_bounds__(kResWarps * 32, 1) resident_kernel(const Resid
                 hwant[r] = !(row_valid && col_valid) && row_near && col_near;
                 int sr = gr;
                 if (torus) sr = sr < 0 ? sr + p.H : (sr >= p.H ? sr - p.H : sr);
-                const bool ld = hwant[r] && sc_ok && (unsigned)sr < (unsigned)p.H;   // else: outside the image = 0
+                // halo columns beside valid rows come from the inbox when that neighbour is a cluster mate
+                const bool from_w = row_valid && gc < vc0 && w_in, from_e = row_valid && gc >= vc1 && e_in;
+                const bool ld = hwant[r] && !from_w && !from_e && sc_ok && (unsigned)sr < (unsigned)p.H;   // else: outside the image = 0
                 hw[r] = res_load8_if(xb + (long long)(ld ? sr : 0) * p.xpitch + (ld ? sc : 0), ld);
+                if (hwant[r] && (from_w || from_e)) {
+                    const int lr = warp * RW + r;
+                    const int slot = from_w ? (gc - (vc0 - HB)) / SB : (gc - vc1) / SB;
+                    hw[r] = inbox[((par * 2 + (from_w ? 0 : 1)) * kRows + lr) * kSlots + slot];
+                }
             }
 #pragma unroll
             for (int r = 0; r < RW; ++r) {
@@ -287,37 +323,104 @@ __global__ void __launch_bounds__(kResWarps * 32, 1) resident_kernel(const Resid
         if (gr >= vr0 && gr < vr1 && col_valid)
             __stcg(reinterpret_cast<uint2 *>(p.dst + (long long)gr * p.dst_pitch + gc), res_pack(E[r], O[r]));
     }
+    if (cx > 1) cluster.sync();   // nobody leaves while a cluster mate may still store into its shared memory
 }
 
 template <int RW>
-cudaError_t launch_rw(const ResidentParams &p, int ch, int k, int ctas, cudaStream_t s) {
-    ResidentParams q = p;
-    void *args[] = {&q};
+cudaError_t launch_rw(const ResidentParams &p, int ch, int k, int ctas, cudaStream_t s, int *cluster_cap) {
     const void *fn =
         k == 16 ? (ch == 1 ? (const void *)resident_kernel<RW, 1, 16> : (const void *)resident_kernel<RW, 3, 16>)
         : k == 8 ? (ch == 1 ? (const void *)resident_kernel<RW, 1, 8> : (const void *)resident_kernel<RW, 3, 8>)
                  : (ch == 1 ? (const void *)resident_kernel<RW, 1, 4> : (const void *)resident_kernel<RW, 3, 4>);
+    // inbox: [2 parities][2 sides][16*RW rows][halo bytes]
+    const size_t smem = (size_t)4 * kResWarps * RW * res_halo_bytes(ch, k);
+    cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    if (p.cx > 8) {   // more than the portable eight CTAs per cluster: B200 allows sixteen on request
+        e = cudaFuncSetAttribute(fn, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+        if (e != cudaSuccess) return e;
+    }
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(ctas);
+    cfg.blockDim = dim3(kResWarps * 32);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = s;
+    cudaLaunchAttribute attr[2];
     // cooperative: the launch fails instead of deadlocking if the CTAs cannot all be resident
-    return cudaLaunchCooperativeKernel(fn, dim3(ctas), dim3(kResWarps * 32), args, 0, s);
+    attr[0].id = cudaLaunchAttributeCooperative;
+    attr[0].val.cooperative = 1;
+    attr[1].id = cudaLaunchAttributeClusterDimension;
+    attr[1].val.clusterDim.x = (unsigned)p.cx;
+    attr[1].val.clusterDim.y = 1;
+    attr[1].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = p.cx > 1 ? 2 : 1;
+    if (cluster_cap) {   // query only: how many clusters of this size can be resident at once
+        int n = 0;
+        e = cudaOccupancyMaxActiveClusters(&n, fn, &cfg);
+        *cluster_cap = e == cudaSuccess ? n : 0;
+        return e;
+    }
+    ResidentParams q = p;
+    void *args[] = {&q};
+    return cudaLaunchKernelExC(&cfg, fn, args);
+}
+
+template <int RW>
+cudaError_t dispatch(const ResidentParams &p, int ch, int k, int ctas, cudaStream_t s, int *cluster_cap) {
+    return launch_rw<RW>(p, ch, k, ctas, s, cluster_cap);
+}
+
+cudaError_t by_rw(const ResidentPlan &plan, const ResidentParams &p, int ch, int ctas, cudaStream_t s, int *cluster_cap) {
+    switch (plan.rw) {
+        case 4: return dispatch<4>(p, ch, plan.k, ctas, s, cluster_cap);
+        case 6: return dispatch<6>(p, ch, plan.k, ctas, s, cluster_cap);
+        case 8: return dispatch<8>(p, ch, plan.k, ctas, s, cluster_cap);
+        case 10: return dispatch<10>(p, ch, plan.k, ctas, s, cluster_cap);
+        case 12: return dispatch<12>(p, ch, plan.k, ctas, s, cluster_cap);
+        case 14: return dispatch<14>(p, ch, plan.k, ctas, s, cluster_cap);
+        case 16: return dispatch<16>(p, ch, plan.k, ctas, s, cluster_cap);
+        default: return cudaErrorInvalidValue;
+    }
 }
 
 }  // namespace
 
 cudaError_t launch_resident(const ResidentPlan &plan, const ResidentParams &p, int ch, cudaStream_t s) {
     const int ctas = plan.strips * plan.ctarows;
-    cudaError_t e = cudaErrorInvalidValue;
-    switch (plan.rw) {
-        case 4: e = launch_rw<4>(p, ch, plan.k, ctas, s); break;
-        case 6: e = launch_rw<6>(p, ch, plan.k, ctas, s); break;
-        case 8: e = launch_rw<8>(p, ch, plan.k, ctas, s); break;
-        case 10: e = launch_rw<10>(p, ch, plan.k, ctas, s); break;
-        case 12: e = launch_rw<12>(p, ch, plan.k, ctas, s); break;
-        case 14: e = launch_rw<14>(p, ch, plan.k, ctas, s); break;
-        case 16: e = launch_rw<16>(p, ch, plan.k, ctas, s); break;
-        default: break;
-    }
+    cudaError_t e = by_rw(plan, p, ch, ctas, s, nullptr);
     count_launch(1);
     return e != cudaSuccess ? e : cudaGetLastError();
+}
+
+// Largest cluster width (CTAs of one tile row sharing halo columns through distributed shared
+// memory) that divides the strip count, is at most 16 (8 is the portable limit, B200 takes 16 on
+// request) and leaves every cluster of the grid resident at once — the kernel's CTAs wait for each other, so all of them
+// have to be on the chip.  1 = no clusters.
+int resident_cluster_width(const ResidentPlan &plan, int ch) {
+    // Opt-in (B200CONV_RES_CLUSTER=1): measured on B200 the cluster path is 4-8 % SLOWER than flags in
+    // L2 alone (profiles/resident_clusters.md) — north/south and diagonal neighbours are in other
+    // clusters, so the L2 handshake stays on the critical path and barrier.cluster comes on top of it.
+    static const bool on = getenv("B200CONV_RES_CLUSTER") && atoi(getenv("B200CONV_RES_CLUSTER")) != 0;
+    if (!on) return 1;
+    static const bool verbose = getenv("B200CONV_RES_DEBUG") && (atoi(getenv("B200CONV_RES_DEBUG")) & 4);
+    const int ctas = plan.strips * plan.ctarows;
+    for (int cx = 16; cx >= 2; --cx) {
+        if (plan.strips % cx) continue;
+        ResidentParams q{};
+        q.cx = cx;
+        int cap = 0;
+        const cudaError_t e = by_rw(plan, q, ch, ctas, nullptr, &cap);
+        if (verbose)
+            fprintf(stderr, "b200conv: resident clusters of %d: %d can be resident, %d needed (%s)\n", cx, cap, ctas / cx,
+                    cudaGetErrorString(e));
+        if (e != cudaSuccess) {
+            cudaGetLastError();
+            continue;
+        }
+        if (cap * cx >= ctas) return cx;
+    }
+    return 1;
 }
 
 }  // namespace b2c

@@ -24,8 +24,10 @@ struct ResidentParams {
     int strips, ctarows;
     int torus;
     int debug;            // profiling switches, 0 in production (see the kernel)
+    int cx;               // cluster width: CTAs of one tile row that trade halo columns through DSMEM (1 = none)
 };
 
 cudaError_t launch_resident(const ResidentPlan &plan, const ResidentParams &p, int ch, cudaStream_t s);
+int resident_cluster_width(const ResidentPlan &plan, int ch);
 
 }  // namespace b2c

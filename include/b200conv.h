@@ -329,7 +329,9 @@ int b2c_blur_device(const uint8_t *d_in, int64_t in_pitch, uint8_t *d_out, int64
  * The work is enqueued on `stream` and the function returns without synchronising.  All
  * calls share the one scratch area: it is cleared at the start of each call, and calls
  * whose GPU work overlaps in time (different streams) race with each other — keep them on
- * one stream or serialise them yourself.  `in_pitch` / `out_pitch` <= 0 mean tight rows. */
+ * one stream or serialise them yourself.  Host threads calling at the same moment are
+ * serialised inside the function while they enqueue, so sharing one stream between threads
+ * is safe.  `in_pitch` / `out_pitch` <= 0 mean tight rows. */
 int b2c_blur_device_noalloc(const uint8_t *d_in, int64_t in_pitch, uint8_t *d_out, int64_t out_pitch,
                             int width, int height, int channels, int repetitions, int boundary,
                             void *stream);

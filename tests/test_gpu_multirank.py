@@ -170,7 +170,7 @@ def test_runs_with_neighbours_replay_as_one_graph():
 def test_halo_profile_counts_waits():
     import b200conv
     img = rnd(128, 512, 3, seed=32)
-    eng = b200conv.Engine(512, 128, 3, boundary="torus", tb=4)
+    eng = b200conv.Engine(512, 128, 3, boundary="torus", tb=4, kernel="stream")
     eng.set_profile(True)
     eng.load(torch.from_numpy(img).cuda())
     eng.exchange()

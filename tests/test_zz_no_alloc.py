@@ -68,6 +68,33 @@ def test_two_calls_in_a_row_match_the_allocating_entry_point(abi):
     assert (got == want).all()
 
 
+def test_device_memory_is_left_alone(abi):
+    """The point of the entry point: no device memory is taken or given back.  After one warm-up
+    call (the first call on a device may load the module that holds the scratch array), the free
+    memory the driver reports must be the same to the byte before and after two more calls —
+    while the allocating entry point, run in between for contrast, is seen to move it."""
+    rng = np.random.default_rng(3)
+    img = rng.integers(0, 256, (1200, 1600, 3), dtype=np.uint8)
+    src = torch.from_numpy(img).cuda().contiguous()
+    out = torch.empty_like(src)
+    stream = torch.cuda.current_stream().cuda_stream
+    h, w = img.shape[0], img.shape[1]
+
+    def call(boundary, reps):
+        rc = abi.b2c_blur_device_noalloc(src.data_ptr(), 0, out.data_ptr(), 0, w, h, 3, reps, boundary, stream)
+        assert rc == 0, abi.b2c_last_error()
+
+    call(ZERO, 3)
+    torch.cuda.synchronize()
+    free0, _ = torch.cuda.mem_get_info()
+    call(TORUS, 12)
+    free_mid, _ = torch.cuda.mem_get_info()      # the work is still in flight: nothing may be held meanwhile either
+    call(ZERO, 7)
+    torch.cuda.synchronize()
+    free1, _ = torch.cuda.mem_get_info()
+    assert free0 == free_mid == free1, (free0, free_mid, free1)
+
+
 def test_matches_the_oracle_too(abi):
     from b200conv import reference_oracle
 
