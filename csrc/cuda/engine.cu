@@ -166,6 +166,9 @@ struct b2c_engine {
     bool courier_on = false;             // the passes being enqueued hand their epochs to the courier
     cudaStream_t side = nullptr;
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    // NVLS: a small symmetric buffer with a multicast mapping, handed in by the caller (b2c_engine_set_nvls)
+    uint32_t *nvls_local = nullptr, *nvls_mc = nullptr;
+    uint32_t nvls_barrier_seq = 0;
 };
 
 namespace {
@@ -459,7 +462,12 @@ int enqueue_pass(b2c_engine *e, const Pass &ps, bool device_epoch, cudaStream_t 
         c.converged = e->pad + kPadConverged;
         c.converged_at = e->pad + kPadConvergedAt;
         c.iters_after = ps.iters_after;
-        CK(launch_converge(c, s));
+        if (e->nvls_mc && n > 1) {
+            NvlsParams nv{e->nvls_local, e->nvls_mc, n, e->rank};
+            CK(launch_converge_nvls(c, nv, s));
+        } else {
+            CK(launch_converge(c, s));
+        }
         e->launches++;
     }
     return B2C_OK;
@@ -1565,6 +1573,13 @@ int b2c_engine_barrier(b2c_engine *e, void *stream) {
         return B2C_EINVAL;
     }
     CK(cudaSetDevice(e->device));
+    if (e->nvls_mc) {
+        NvlsParams nv{e->nvls_local, e->nvls_mc, n, e->rank};
+        CK(launch_barrier_nvls(nv, ++e->nvls_barrier_seq, reinterpret_cast<unsigned long long *>(e->pad + kPadBarrierSkew),
+                               (cudaStream_t)stream));
+        e->launches++;
+        return B2C_OK;
+    }
     BarrierParams b{};
     b.slots = e->pad + kPadBarrier;
     for (int k = 0; k < n; ++k) b.peer_slots[k] = e->rank_pad[k] + kPadBarrier;
@@ -1574,6 +1589,21 @@ int b2c_engine_barrier(b2c_engine *e, void *stream) {
     b.skew_cycles = reinterpret_cast<unsigned long long *>(e->pad + kPadBarrierSkew);
     CK(launch_barrier(b, (cudaStream_t)stream));
     e->launches++;
+    return B2C_OK;
+}
+
+// NVLS multicast (collective; the caller owns the memory): `local` is this rank's replica of a
+// zero-initialised symmetric buffer of at least 64 words, `mc` its multicast address.  From then
+// on the convergence OR and the start barrier are one multimem.red each.  Pass nulls to go back to
+// peer stores.
+int b2c_engine_set_nvls(b2c_engine *e, uint32_t *local, uint32_t *mc, int words) {
+    if (!e || (local == nullptr) != (mc == nullptr) || (local && words < kNvlsWords)) {
+        set_error("engine_set_nvls: need both pointers and at least %d words", kNvlsWords);
+        return B2C_EINVAL;
+    }
+    e->nvls_local = local;
+    e->nvls_mc = mc;
+    e->nvls_barrier_seq = 0;
     return B2C_OK;
 }
 

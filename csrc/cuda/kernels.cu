@@ -373,6 +373,65 @@ __global__ void barrier_kernel(const BarrierParams b) {
 
 __global__ void courier_kernel(const CourierParams c) { courier_loop(c, threadIdx.x, 0u); }
 
+// ---- NVLS: reductions in the switch (replaces MPI_Allreduce / MPI_Barrier, mpi_convolution.c:151,264-275)
+
+__device__ __forceinline__ void multimem_red_add(uint32_t *mc, uint32_t v) {
+    asm volatile("multimem.red.release.sys.global.add.u32 [%0], %1;" ::"l"(mc), "r"(v) : "memory");
+}
+
+// Convergence OR over all ranks: ONE multimem.red (bit + arrival count in one word) and ONE poll of
+// the local replica, instead of N peer stores and N polls.
+__global__ void converge_nvls_kernel(const ConvergeParams c, const NvlsParams n) {
+    if (threadIdx.x != 0) return;
+    const unsigned mine = *c.changed;
+    *c.changed = 0;
+    const int slot = kNvlsConvergeWord + (int)(c.seq & 1u);
+    multimem_red_add(n.mc + slot, 0x10000u + (mine ? 1u : 0u));
+    const long long t0 = clock64();
+    uint32_t v;
+    while (((v = ld_relaxed_sys(n.local + slot)) >> 16) != (uint32_t)n.nranks) {
+        if (clock64() - t0 > (20ll << 30)) {
+            printf("b200conv: NVLS convergence wait timeout rank=%d have=%#x\n", n.rank, v);
+            __trap();
+        }
+    }
+    // every rank's contribution to this replica has arrived: clear it for check seq+2 (nobody can be
+    // that far ahead — check seq+1 needs this rank's contribution, which comes after this store)
+    n.local[slot] = 0;
+    __threadfence_system();
+    if (!(v & 0xffffu) && !*c.converged) {
+        *c.converged = 1;
+        *c.converged_at = c.iters_after;
+    }
+}
+
+cudaError_t launch_converge_nvls(const ConvergeParams &c, const NvlsParams &n, cudaStream_t s) {
+    converge_nvls_kernel<<<1, 32, 0, s>>>(c, n);
+    count_launch(1);
+    return cudaGetLastError();
+}
+
+__global__ void barrier_nvls_kernel(const NvlsParams n, const uint32_t seq, unsigned long long *skew_cycles) {
+    if (threadIdx.x != 0) return;
+    const long long t0 = clock64();
+    multimem_red_add(n.mc + kNvlsBarrierWord, 1u);
+    const uint32_t want = seq * (uint32_t)n.nranks;
+    while ((int)(ld_relaxed_sys(n.local + kNvlsBarrierWord) - want) < 0) {
+        if (clock64() - t0 > (20ll << 30)) {
+            printf("b200conv: NVLS start barrier timeout rank=%d\n", n.rank);
+            __trap();
+        }
+    }
+    (void)ld_acquire_sys(n.local + kNvlsBarrierWord);
+    if (skew_cycles) *skew_cycles = (unsigned long long)(clock64() - t0);
+}
+
+cudaError_t launch_barrier_nvls(const NvlsParams &n, uint32_t seq, unsigned long long *skew_cycles, cudaStream_t s) {
+    barrier_nvls_kernel<<<1, 32, 0, s>>>(n, seq, skew_cycles);
+    count_launch(1);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_courier(const CourierParams &c, cudaStream_t s) {
     courier_kernel<<<1, 32, 0, s>>>(c);
     count_launch(1);

@@ -72,6 +72,21 @@ struct BarrierParams {
 };
 cudaError_t launch_barrier(const BarrierParams &b, cudaStream_t s);
 
+// NVLS variants (the box exposes multicast: one multimem.red lands in every rank's replica of a small
+// symmetric buffer, reduced in the switch).  Word layout of that buffer, in 32-bit words:
+//   [0], [1]   convergence slots by check parity: sum over ranks of (0x10000 + changed bit)
+//   [32]       start-barrier arrivals (never reset: the n-th barrier waits for n * nranks)
+constexpr int kNvlsConvergeWord = 0;
+constexpr int kNvlsBarrierWord = 32;
+constexpr int kNvlsWords = 64;
+struct NvlsParams {
+    uint32_t *local;   // this rank's replica
+    uint32_t *mc;      // multicast address of the same buffer
+    int nranks, rank;
+};
+cudaError_t launch_converge_nvls(const ConvergeParams &c, const NvlsParams &n, cudaStream_t s);
+cudaError_t launch_barrier_nvls(const NvlsParams &n, uint32_t seq, unsigned long long *skew_cycles, cudaStream_t s);
+
 struct CourierParams;   // stencil_stream.cuh
 cudaError_t launch_courier(const CourierParams &c, cudaStream_t s);
 

@@ -269,6 +269,13 @@ int b2c_engine_tune_set(b2c_engine *e, int i);
  * mpi_convolution.c:151): work enqueued on `stream` after it starts within microseconds on all
  * ranks.  Collective.  barrier_wait_cycles: SM clocks this rank spent in the last one (synchronises). */
 int b2c_engine_barrier(b2c_engine *e, void *stream);
+/* NVLS multicast for the two collectives (replaces MPI_Barrier / the max-reduction's role of
+ * mpi_convolution.c:151,264-275): `local` = this rank's replica of a zero-initialised symmetric
+ * buffer of >= 64 32-bit words that every rank of the grid has mapped, `mc` = its multicast address
+ * (e.g. from torch.distributed._symmetric_memory).  Afterwards the convergence OR and
+ * b2c_engine_barrier are one multimem.red.add + one poll.  Collective; the caller keeps the memory
+ * alive; nulls switch back to peer stores. */
+int b2c_engine_set_nvls(b2c_engine *e, uint32_t *local, uint32_t *mc, int words);
 int64_t b2c_engine_barrier_wait_cycles(b2c_engine *e);
 
 /* Opt-in wait-time counters of the halo protocol (also B200CONV_HALO_PROF=1): 40 words,

@@ -101,6 +101,7 @@ def _load() -> C.CDLL:
         "b2c_engine_tune_time": (C.c_double, [P, I, V]),
         "b2c_engine_tune_set": (I, [P, I]),
         "b2c_engine_barrier": (I, [P, V]),
+        "b2c_engine_set_nvls": (I, [P, V, V, I]),
         "b2c_engine_barrier_wait_cycles": (L, [P]),
         "b2c_engine_set_profile": (I, [P, I]),
         "b2c_engine_halo_profile": (I, [P, C.POINTER(C.c_uint64 * 40), I]),

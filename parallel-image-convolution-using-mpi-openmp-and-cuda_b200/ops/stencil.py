@@ -156,6 +156,11 @@ class Engine:
         """Device-side barrier over peer memory (collective)."""
         check(lib.b2c_engine_barrier(self._h, _stream_ptr(stream)), "engine_barrier")
 
+    def set_nvls(self, local_ptr: int, multicast_ptr: int, words: int):
+        """Use an NVLS multicast mapping of a small symmetric buffer for the convergence OR and the
+        start barrier (collective; the caller keeps the buffer alive)."""
+        check(lib.b2c_engine_set_nvls(self._h, local_ptr or None, multicast_ptr or None, int(words)), "engine_set_nvls")
+
     def barrier_wait_cycles(self) -> int:
         return check(lib.b2c_engine_barrier_wait_cycles(self._h), "engine_barrier_wait_cycles")
 

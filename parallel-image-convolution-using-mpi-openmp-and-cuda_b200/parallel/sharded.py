@@ -20,6 +20,7 @@ from .decomposition import decompose
 class ShardedBlur:
     def __init__(self, width, height, channels, group=None, grid=None, device=None, **opts):
         self.tuned = None
+        self.nvls = False
         if not dist.is_initialized():
             raise RuntimeError("torch.distributed is not initialised")
         self.group = group
@@ -37,9 +38,40 @@ class ShardedBlur:
             allh = [torch.empty(HANDLE_BYTES, dtype=torch.uint8, device=mine.device) for _ in range(self.world)]
             dist.all_gather(allh, mine, group=group)
             self.engine.import_handles([bytes(t.cpu().numpy().tobytes()) for t in allh])
+            self.nvls = self._setup_nvls()
             self.tuned = self._tune_coupled()
         self._ev0 = torch.cuda.Event(enable_timing=True)
         self._ev1 = torch.cuda.Event(enable_timing=True)
+
+    def _setup_nvls(self) -> bool:
+        """NVLS multicast for the two collectives, when the box exposes it: a 256-word symmetric
+        buffer from torch's symmetric memory (which does the cuMulticast plumbing); the engine then
+        issues one ``multimem.red`` per convergence check / start barrier instead of one peer store
+        and one poll per rank.  ``B200CONV_NVLS=0`` keeps the peer stores."""
+        import os
+
+        ok = 0
+        if os.environ.get("B200CONV_NVLS", "1") != "0":
+            try:
+                import torch.distributed._symmetric_memory as symm_mem
+
+                buf = symm_mem.empty(256, dtype=torch.uint32, device=f"cuda:{self.device}")
+                buf.zero_()
+                hdl = symm_mem.rendezvous(buf, group=self.group if self.group is not None else dist.group.WORLD)
+                mc = int(getattr(hdl, "multicast_ptr", 0) or 0)
+                if mc:
+                    self._nvls_buf, self._nvls_hdl, self._nvls_mc = buf, hdl, mc
+                    ok = 1
+            except Exception:  # noqa: BLE001  (no symmetric memory / no multicast on this box)
+                ok = 0
+        # all ranks or none
+        flag = torch.tensor([ok], dtype=torch.int32, device=f"cuda:{self.device}")
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=self.group)
+        torch.cuda.synchronize(self.device)
+        if int(flag.item()) == 1:
+            self.engine.set_nvls(self._nvls_buf.data_ptr(), self._nvls_mc, 256)
+            return True
+        return False
 
     def _tune_coupled(self):
         """Rows per warp are chosen by timing a few candidates with the halo exchange live, all
