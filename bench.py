@@ -131,7 +131,9 @@ def run_b200conv(a):
             dist.all_reduce(t, op=dist.ReduceOp.SUM)
         return float(t.item())
 
-    # ---- device-timed loop: K steps of `reps` iterations on resident data
+    # ---- device-timed loop: K steps of `reps` iterations on resident data, on a stream of its own
+    #      (on the legacy default stream a run can neither be replayed as a CUDA graph nor have a courier)
+    torch.cuda.set_stream(torch.cuda.Stream())
     load()
     for _ in range(a.warmup):
         core.run(a.reps)

@@ -56,26 +56,33 @@ def digest(path: Path, extra: str) -> str:
     return h.hexdigest()[:16]
 
 
-def compile_one(src: str, force: bool) -> Path:
+def compile_one(src: str, force: bool, extra=(), bdir: Path = None) -> Path:
+    bdir = bdir or BUILD
     sp = ROOT / src
-    tag = digest(sp, " ".join(NVCC_FLAGS))
-    obj = BUILD / (sp.stem + "." + tag + ".o")
+    flags = [*NVCC_FLAGS, *extra]
+    tag = digest(sp, " ".join(flags))
+    obj = bdir / (sp.stem + "." + tag + ".o")
     if obj.exists() and not force:
         return obj
-    for old in BUILD.glob(sp.stem + ".*.o"):
+    for old in bdir.glob(sp.stem + ".*.o"):
         old.unlink()
-    run([NVCC, *NVCC_FLAGS, "-c", str(sp), "-o", str(obj)], log=BUILD / (sp.stem + ".ptxas.log"))
+    run([NVCC, *flags, "-c", str(sp), "-o", str(obj)], log=bdir / (sp.stem + ".ptxas.log"))
     return obj
 
 
-def build_core(force=False) -> Path:
-    BUILD.mkdir(exist_ok=True)
+def build_core(force=False, debug=False) -> Path:
+    """debug=True: lib/libb200conv_core_debug.so with -DB2C_DEBUG — every global / peer address the
+    streaming kernels form is checked against its allocation and epochs are checked for running
+    ahead (stencil_stream.cuh); load it with B200CONV_DEBUG_LIB=1.  Stands in for compute-sanitizer."""
+    bdir = BUILD / "debug" if debug else BUILD
+    bdir.mkdir(parents=True, exist_ok=True)
     LIB.mkdir(parents=True, exist_ok=True)
     srcs = [s for s in CORE_SOURCES if (ROOT / s).exists()]
+    extra = ("-DB2C_DEBUG",) if debug else ()
     with cf.ThreadPoolExecutor(max_workers=min(8, len(srcs))) as ex:
-        objs = list(ex.map(lambda s: compile_one(s, force), srcs))
-    out = LIB / "libb200conv_core.so"
-    stamp = BUILD / "core.link"
+        objs = list(ex.map(lambda s: compile_one(s, force, extra, bdir), srcs))
+    out = LIB / ("libb200conv_core_debug.so" if debug else "libb200conv_core.so")
+    stamp = bdir / "core.link"
     key = " ".join(o.name for o in objs)
     if force or not out.exists() or not stamp.exists() or stamp.read_text() != key:
         run([NVCC, "-shared", *ARCH, "-o", str(out), *map(str, objs), "-lpthread", "-ldl", "-lrt"])
@@ -141,7 +148,10 @@ if __name__ == "__main__":
     ap = argparse.ArgumentParser()
     ap.add_argument("--force", action="store_true")
     ap.add_argument("--no-torch", action="store_true")
+    ap.add_argument("--debug", action="store_true", help="also build lib/libb200conv_core_debug.so (-DB2C_DEBUG)")
     a = ap.parse_args()
+    if a.debug:
+        print(build_core(a.force, debug=True), "ok")
     for p in build_all(a.force, not a.no_torch):
         if p is not None:
             print(p, "ok" if p.exists() else "skipped")

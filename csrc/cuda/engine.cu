@@ -164,6 +164,7 @@ struct b2c_engine {
     // courier (kernels.cu): forwards halo epochs to peers on other devices from a side stream
     bool remote_peers = false;           // some neighbour lives on another device
     bool courier_on = false;             // the passes being enqueued hand their epochs to the courier
+    unsigned preloaded = 0;              // bit k: the k-stage pass kernel of this plan is loaded
     cudaStream_t side = nullptr;
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     // NVLS: a small symmetric buffer with a multicast mapping, handed in by the caller (b2c_engine_set_nvls)
@@ -176,6 +177,7 @@ namespace {
 // Forget everything that was built from the current plan or peer wiring (CUDA graphs, the
 // persistent kernel's pass tables).  The caller has made sure nothing of it is still running.
 void drop_graphs(b2c_engine *e) {
+    e->preloaded = 0;
     for (auto &g : e->graphs) cudaGraphExecDestroy(g.second);
     e->graphs.clear();
     if (!e->persist.empty()) {
@@ -365,6 +367,11 @@ void fill_push_params(const b2c_engine *e, int buf_i, bool device_epoch, PushPar
     q.counters = e->pad + kPadCounters;
     q.post_epoch = (device_epoch ? e->epoch - e->epoch_dev : e->epoch) + 1;
     q.epoch_base = device_epoch ? e->pad + kPadEpoch : nullptr;
+#ifdef B2C_DEBUG
+    q.dbg_before = (long long)kFrameRows * e->pitch + kLeftPad;
+    q.dbg_after = e->alloc_bytes - q.dbg_before;
+    q.dbg_rank = e->rank;
+#endif
     q.wait_epoch_valid = 0;   // the pass in front of a push has waited for everything the push needs
     q.converged = nullptr;    // only the per-pass fallback push (enqueue_pass) follows the convergence latch
     for (int d = 0; d < 8; ++d) {
@@ -496,6 +503,14 @@ int courier_begin(b2c_engine *e, const std::vector<Pass> &passes, bool device_ep
         if (ps.group_end) groups++;
     }
     if (groups == 0) return B2C_OK;
+    // every kernel that will be launched while the courier spins must be loaded by now (lazy module
+    // loading waits for running kernels: kernels.cu, preload_stream_kernel)
+    for (const Pass &ps : passes) {
+        if (e->preloaded & (1u << ps.k)) continue;
+        CK(e->kernel == B2C_KERNEL_TMA ? preload_stream_tma_kernel(ps.k, e->SB, e->CH, false)
+                                       : preload_stream_kernel(ps.k, e->SB, e->CH, false));
+        e->preloaded |= 1u << ps.k;
+    }
     if (!e->side) {
         CK(cudaStreamCreateWithFlags(&e->side, cudaStreamNonBlocking));
         CK(cudaEventCreateWithFlags(&e->ev_fork, cudaEventDisableTiming));

@@ -28,6 +28,10 @@ template <int K, int NW, int CH>
 static cudaError_t stream_op_t(int op, const PassParams *p, bool check, cudaStream_t s, int *occ) {
     auto fn = check ? stream_kernel<K, NW, CH, true> : stream_kernel<K, NW, CH, false>;
     if (op == 1) return cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, fn, kWarpsPerCta * 32, 0);
+    if (op == 2) {   // make sure the function is loaded (see preload_stream_kernel)
+        cudaFuncAttributes fa;
+        return cudaFuncGetAttributes(&fa, fn);
+    }
     const int warps = p->nbands * p->nchunks;
     const int ctas = (warps + kWarpsPerCta - 1) / kWarpsPerCta;
     // Programmatic dependent launch: the next pass may start scheduling CTAs while this one
@@ -69,6 +73,15 @@ bool stream_config_ok(int k, int strip_bytes) {
 
 cudaError_t launch_stream(const PassParams &p, int k, int strip_bytes, int ch, bool check, cudaStream_t s) {
     return stream_op(0, &p, k, strip_bytes, ch, check, s, nullptr);
+}
+
+// With lazy module loading (the CUDA default) the first launch of a kernel loads it, and loading
+// may wait for every kernel that is running on the device.  A pass variant that is first needed
+// while the courier kernel spins (k = 2 or 1 at the end of a run) would therefore never load:
+// the courier waits for that pass, the load waits for the courier.  So every variant a run uses
+// is loaded before the courier starts.
+cudaError_t preload_stream_kernel(int k, int strip_bytes, int ch, bool check) {
+    return stream_op(2, nullptr, k, strip_bytes, ch, check, nullptr, nullptr);
 }
 
 int stream_occupancy(int k, int strip_bytes, int ch) {
@@ -232,6 +245,10 @@ __global__ void halo_push_kernel(const PushParams q) {
     for (int r = r_lo; r < r_hi; ++r) {
         const uint8_t *s = q.src + (long long)(sr0 + r) * q.pitch + sc0;
         uint8_t *t = q.peer_dst[d] + (long long)(sr0 + r - dr * q.rows) * q.pitch + (sc0 - dc * (long long)q.bw);
+#ifdef B2C_DEBUG
+        B2C_DBG_RANGE("push source", q.dbg_rank, s, nc, q.src - q.dbg_before, q.src + q.dbg_after);
+        B2C_DBG_RANGE("push target", q.dbg_rank, t, nc, q.peer_dst[d] - q.dbg_before, q.peer_dst[d] + q.dbg_after);
+#endif
         const bool al = (((uintptr_t)s | (uintptr_t)t) & 15) == 0;
         if (al) {
             const long long n16 = nc / 16;

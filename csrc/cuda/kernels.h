@@ -29,6 +29,10 @@ struct PushParams {
     const uint32_t *epoch_base;      // device word holding the epoch at the start of the run (null: 0)
     uint32_t *epoch_word;            // when set, block (0,0) stores post_epoch there (initial exchange)
     const unsigned int *converged;   // when set and non-zero the push is skipped (like the passes)
+#ifdef B2C_DEBUG
+    long long dbg_before, dbg_after; // bytes of an allocation before / after its interior origin
+    int dbg_rank;
+#endif
 };
 
 constexpr int kMaxRanks = 64;
@@ -48,7 +52,8 @@ __host__ __device__ inline int kDirDrDev(int d) { return d == 0 || d == 4 || d =
 __host__ __device__ inline int kDirDcDev(int d) { return d == 2 || d == 4 || d == 6 ? -1 : (d == 3 || d == 5 || d == 7 ? 1 : 0); }
 
 bool stream_config_ok(int k, int strip_bytes);
-int stream_occupancy(int k, int strip_bytes, int ch);  // resident CTAs (of kWarpsPerCta warps) per SM
+int stream_occupancy(int k, int strip_bytes, int ch);
+cudaError_t preload_stream_kernel(int k, int strip_bytes, int ch, bool check);   // load the variant now (lazy loading)  // resident CTAs (of kWarpsPerCta warps) per SM
 cudaError_t launch_stream(const PassParams &p, int k, int strip_bytes, int ch, bool check, cudaStream_t s);
 // Persistent dataflow kernel (stencil_stream.cuh): every pass of a run in one launch of `ctas` CTAs.
 cudaError_t launch_stream_persist(const PersistParams &q, int k, int strip_bytes, int ch, int ctas, cudaStream_t s);

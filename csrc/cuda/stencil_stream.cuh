@@ -110,7 +110,7 @@ struct alignas(16) PassParams {
 // Debug build (python build.py --debug): every global address the streaming kernels form is checked
 // against the allocation it must fall into, epochs are checked for monotonicity; a violation prints
 // rank / what / address and traps.  Stands in for compute-sanitizer where that tool is not available.
-__device__ __noinline__ void dbg_fail(const char *what, int rank, const void *p, const void *lo, const void *hi) {
+static __device__ __noinline__ void dbg_fail(const char *what, int rank, const void *p, const void *lo, const void *hi) {
     printf("b200conv DEBUG: rank %d: %s address %p outside [%p, %p)\n", rank, what, p, lo, hi);
     __trap();
 }

@@ -226,6 +226,7 @@ static cudaError_t tma_op_t(int op, TmaState *t, const PassParams *p, int src_in
         cfg = true;
     }
     if (op == 1) return cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ_out, fn, kWarpsPerCta * 32, smem);
+    if (op == 2) return cudaSuccess;   // cudaFuncSetAttribute above has loaded the function
     const int warps = p->nbands * p->nchunks;
     const int ctas = (warps + kWarpsPerCta - 1) / kWarpsPerCta;
     // programmatic dependent launch, as for the LDG kernel (kernels.cu)
@@ -261,6 +262,10 @@ static cudaError_t tma_op(int op, TmaState *t, const PassParams *p, int src_inde
 cudaError_t launch_stream_tma(TmaState *t, const PassParams &p, int src_index, int k, int strip_bytes, int ch,
                               bool check, cudaStream_t s) {
     return tma_op(0, t, &p, src_index, k, strip_bytes, ch, check, s, nullptr);
+}
+
+cudaError_t preload_stream_tma_kernel(int k, int strip_bytes, int ch, bool check) {
+    return tma_op(2, nullptr, nullptr, 0, k, strip_bytes, ch, check, nullptr, nullptr);
 }
 
 int stream_tma_occupancy(int k, int strip_bytes, int ch) {

@@ -18,6 +18,7 @@ void tma_destroy(TmaState *t);
 cudaError_t launch_stream_tma(TmaState *t, const PassParams &p, int src_index, int k, int strip_bytes, int ch,
                               bool check, cudaStream_t s);
 
-int stream_tma_occupancy(int k, int strip_bytes, int ch);  // resident CTAs per SM with its shared-memory ring
+int stream_tma_occupancy(int k, int strip_bytes, int ch);
+cudaError_t preload_stream_tma_kernel(int k, int strip_bytes, int ch, bool check);   // load the variant now (lazy loading)  // resident CTAs per SM with its shared-memory ring
 
 }  // namespace b2c

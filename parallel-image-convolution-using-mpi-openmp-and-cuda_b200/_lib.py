@@ -14,7 +14,9 @@ from pathlib import Path
 
 PKG_DIR = Path(__file__).resolve().parent
 ROOT = PKG_DIR.parent
-LIB_PATH = PKG_DIR / "lib" / "libb200conv_core.so"
+# B200CONV_DEBUG_LIB=1: the -DB2C_DEBUG build (python build.py --debug) with address / epoch checks in the kernels
+LIB_PATH = PKG_DIR / "lib" / ("libb200conv_core_debug.so" if os.environ.get("B200CONV_DEBUG_LIB", "0") not in ("", "0")
+                              else "libb200conv_core.so")
 LAUNCHER_PATH = PKG_DIR / "lib" / "b200conv"
 HANDLE_BYTES = 256
 
