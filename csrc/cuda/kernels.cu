@@ -259,14 +259,15 @@ __global__ void halo_push_kernel(const PushParams q) {
             for (long long i = threadIdx.x; i < nc; i += blockDim.x) t[i] = s[i];
         }
     }
-    __threadfence_system();
+    // every thread's stores are ordered before the count-in at GPU scope; only the last CTA of a
+    // direction pays for the system-scope fence in front of the flag (cumulative, see halo_publish)
+    __threadfence();
     __syncthreads();
     if (threadIdx.x == 0) {
         const unsigned old = atomicAdd(q.counters + d * 32, 1u);
         if (old + 1 == gridDim.x) {
             q.counters[d * 32] = 0;
-            __threadfence_system();
-            st_release_sys(q.peer_flag[d], q.post_epoch + base);
+            st_release_sys(q.peer_flag[d], q.post_epoch + base);   // its fence is also the acquire side of the atomic
         }
     }
 }

@@ -96,7 +96,7 @@ struct alignas(16) PassParams {
     unsigned int *changed;  // CHECK: OR-accumulated "last stage changed a byte"
     const unsigned int *converged;  // when set (non-null and non-zero) the pass is skipped
     int org_x, org_y;       // position of src/dst (0,0) inside the allocation (bytes, rows): TMA coordinates
-    int raster;             // 1: chunk-major work order instead of ring-first
+    int raster;             // work order: 0 ring-first, 1 chunk-major, 2 ring-LAST (ring-first reversed)
 #ifdef B2C_DEBUG
     const uint8_t *dbg_src_lo, *dbg_src_hi;   // [lo, hi) of the source / destination allocation
     uint8_t *dbg_dst_lo, *dbg_dst_hi;
@@ -540,9 +540,9 @@ __device__ __forceinline__ void halo_wait(const HaloParams &h, const unsigned dm
 // copies are in flight (it also waits for the host side), and a pass cannot end before its slowest
 // thread: with the fence inside the pass, 8 GPUs lost 4-6 ms per 1000 iterations end to end
 // (profiles/e2e_probe.md).  So with peers on other devices the last arriver only stores the epoch
-// into a local word (release, GPU scope); a one-warp courier kernel on a side stream acquires it,
-// executes fence.sc.sys — cumulative over everything that happened before in causality order, i.e.
-// every ring warp's stores — and release-stores the flag into the neighbour.  Without a courier
+// into a local word (release, GPU scope); a one-warp courier kernel on a side stream acquires it
+// and release-stores the flag into the neighbour at system scope — cumulative over everything
+// that happened before in causality order, i.e. every ring warp's stores.  Without a courier
 // (peers on this device, one-shot paths) the last arriver publishes itself.
 __device__ __forceinline__ void halo_publish(const HaloParams &h, const unsigned dmask, const uint32_t E,
                                              const int lane, const bool data) {
@@ -619,7 +619,10 @@ __device__ __forceinline__ void stream_tile(const PassParams &p, const int band,
 template <int K, int NW, int CH, bool CHECK, class MakeFeed>
 __device__ __forceinline__ void stream_warp(const PassParams &p, const int wid, const int lane, MakeFeed make_feed) {
     int band, chunk;
-    map_work(wid, p.nbands, p.nchunks, p.raster ? p.nbands : p.halo.nbw, p.halo.nbe, band, chunk);
+    // Order 2: a pass that only WAITS for the neighbours' rings (the first pass of a group) takes its
+    // ring items last, so that the epoch has the whole interior's time to arrive.
+    map_work(p.raster == 2 ? p.nbands * p.nchunks - 1 - wid : wid, p.nbands, p.nchunks,
+             p.raster == 1 ? p.nbands : p.halo.nbw, p.halo.nbe, band, chunk);
 
     // Programmatic dependent launch: everything above ran while the previous pass was still
     // draining.  Let the pass after this one start scheduling, then wait until the previous
@@ -676,7 +679,10 @@ __device__ __forceinline__ void courier_loop(const CourierParams &c, const int l
     while ((int)(sent - last) < 0) {
         const uint32_t v = ld_acquire_gpu(src);
         if ((int)(v - sent) > 0 && (int)(v - last) <= 0) {
-            __threadfence_system();    // fence.sc.sys: cumulative over the ring warps' stores
+            // The acquire above synchronises with the last arriver's release (GPU scope); the release
+            // store's own system-scope fence is cumulative over everything that happened before it,
+            // i.e. every ring warp's stores.  ONE system-scope fence: a second one in front of it
+            // doubles the latency the neighbours see while PCIe copies are in flight.
             st_release_sys(dst, v);
             sent = v;
             t0 = clock64();
@@ -772,7 +778,7 @@ stream_persist_kernel(const PersistParams q) {
             __syncwarp();
         }
         int band, chunk;
-        map_work((int)(g - lo), p.nbands, p.nchunks, p.raster ? p.nbands : p.halo.nbw, p.halo.nbe, band, chunk);
+        map_work((int)(g - lo), p.nbands, p.nchunks, p.raster == 1 ? p.nbands : p.halo.nbw, p.halo.nbe, band, chunk);
         const long long c0 = q.prof ? clock64() : 0;
         if (t > 0) {
             // lanes 0-8: the 3x3 neighbourhood in the previous pass's tiling
