@@ -18,8 +18,10 @@
 //     it pushes;
 //   * ring results are published before the interior is written (the GPU orders ring warps first);
 //   * a check pass is followed by an all-to-all exchange of one "changed" bit through per-rank
-//     slots tagged with the check number and double-buffered by its parity; when nobody changed,
-//     every rank latches `converged` and skips the remaining passes.
+//     slots tagged with the check number and double-buffered by its parity; when nobody changed
+//     at check c, every rank still runs interval c+1 (on the GPU the reduction of check c is in
+//     flight on a side stream meanwhile — the image is a fixed point, so nothing changes) and
+//     skips everything from interval c+2 on.
 //
 // Random sleeps can be injected at every point where the GPU ranks may drift apart.  Built with
 // -fsanitize=thread (tests/test_halo_model.py) the model shows that the protocol has no data race
@@ -58,6 +60,7 @@ struct Pass {
     int ext;         // iterations left in the group after this pass
     int mode;
     bool group_end;
+    int interval;    // check interval (1-based; 0 without check_every)
 };
 
 // Same rule as make_passes() in engine.cu: groups of at most F iterations (a group also ends on
@@ -84,7 +87,8 @@ std::vector<Pass> split_passes(int reps, int K, int F, int ce) {
             if (j == 0) mode |= kWaitData;
             if (n >= 2 && j == n - 2) mode |= kPostAck;
             if (j == n - 1) mode |= kPush | (n >= 2 ? kWaitAck : 0);
-            v.push_back({ks[j], j == n - 1 && ce > 0 && done % ce == 0, done, ext, mode, j == n - 1});
+            v.push_back({ks[j], j == n - 1 && ce > 0 && done % ce == 0, done, ext, mode, j == n - 1,
+                         ce > 0 ? (done - 1) / ce + 1 : 0});
         }
     }
     return v;
@@ -157,7 +161,7 @@ struct World {
         uint32_t epoch = 0;
         int cur = 0;
         uint32_t seq = 0;
-        bool converged = false;
+        int conv_check = 0;   // number of the check that found the fixed point
         std::vector<uint8_t> t0, t1;
         me.iters = passes.empty() ? 0 : passes.back().iters_after;
         const int nimg = std::max(1, o.images);
@@ -183,7 +187,8 @@ struct World {
 
         for (const Pass &ps : passes) {
             unsigned changed = 0;
-            if (!converged) {
+            const bool skip = conv_check != 0 && ps.interval > conv_check + 1;
+            if (!skip) {
                 jitter();
                 if (ps.mode & kWaitData)
                     for (int d = 0; d < 8; ++d)
@@ -237,7 +242,7 @@ struct World {
                 cur ^= 1;
                 if (ps.group_end) epoch++;
             }
-            if (ps.check) {
+            if (ps.check && !skip) {
                 ++seq;
                 const uint32_t tag = seq * 2u;
                 const int set = o.single_slot_set ? 0 : (int)(seq & 1u) * n;
@@ -254,8 +259,8 @@ struct World {
                         return;
                     any |= v & 1u;
                 }
-                if (!any && !converged) {
-                    converged = true;
+                if (!any && conv_check == 0) {
+                    conv_check = ps.interval;
                     me.iters = ps.iters_after;
                 }
             }

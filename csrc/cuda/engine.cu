@@ -46,9 +46,9 @@ struct NvtxRange {
 constexpr int kPadFlags = 0;          // 8 x 32: data epochs, index = direction the ring came from
 constexpr int kPadCounters = 256;     // 8 x 32: ring-warp arrival counters
 constexpr int kPadSlots = 512;        // 2 parities x kMaxRanks words (convergence bits)
-constexpr int kPadChanged = 640;
-constexpr int kPadConverged = 641;
-constexpr int kPadConvergedAt = 642;
+constexpr int kPadChanged = 640;      // 2 words: "a byte changed", by check parity (the reduction of a check runs beside the next interval)
+constexpr int kPadConverged = 642;    // number of the check that found the fixed point (0: none)
+constexpr int kPadConvergedAt = 643;
 constexpr int kPadEpoch = 672;        // the epoch at the start of the current run (device-side mirror of e->epoch)
 constexpr int kPadBarrier = 704;      // kMaxRanks words: start-barrier sequence numbers, index = rank
 constexpr int kPadBarrierSkew = 768;  // 2 words (u64): cycles this rank waited in the last start barrier
@@ -73,6 +73,7 @@ static_assert(sizeof(Blob) <= B2C_HANDLE_BYTES, "blob too large");
 // exchanged once per group (see HaloParams in stencil_stream.cuh).
 struct Pass {
     int k;                 // fused iterations
+    unsigned interval;     // check interval the pass belongs to (1-based; 0 without check_every)
     bool check;            // convergence check after this pass (always the last pass of its group)
     unsigned iters_after;  // iterations completed after it, counted from the start of the run
     int ext;               // iterations left in the group after this pass = how far the block is extended
@@ -136,6 +137,7 @@ struct b2c_engine {
     std::vector<Pass> staged;   // b2c_engine_plan_run / b2c_engine_run_pass
     // plan
     int kernel = B2C_KERNEL_STREAM, K = 4, SB = 16, F = 1;
+    int SB0 = 0;                     // strip width of the modelled plan (coupled tuning may change SB)
     bool chunk_rows_fixed = false;   // the caller gave chunk_rows: never tuned
     int sm_count = 148;
     long long delay = 0;
@@ -167,6 +169,8 @@ struct b2c_engine {
     unsigned preloaded = 0;              // bit k: the k-stage pass kernel of this plan is loaded
     cudaStream_t side = nullptr;
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    cudaEvent_t ev_check[2] = {nullptr, nullptr};   // reduction of a convergence check done, by check parity
+    bool check_pending[2] = {false, false};
     // NVLS: a small symmetric buffer with a multicast mapping, handed in by the caller (b2c_engine_set_nvls)
     uint32_t *nvls_local = nullptr, *nvls_mc = nullptr;
     uint32_t nvls_barrier_seq = 0;
@@ -317,8 +321,9 @@ void fill_pass_params(const b2c_engine *e, const Pass &ps, int src_i, bool devic
     p.zero_s = zero && e->nb[B2C_S] < 0;
     p.zero_w = zero && e->nb[B2C_W] < 0;
     p.zero_e = zero && e->nb[B2C_E] < 0;
-    p.changed = ps.check ? e->pad + kPadChanged : nullptr;
+    p.changed = ps.check ? e->pad + kPadChanged + (ps.interval & 1u) : nullptr;
     p.converged = e->opts.check_every > 0 ? e->pad + kPadConverged : nullptr;
+    p.interval = ps.interval;
 #ifdef B2C_DEBUG
     p.dbg_src_lo = e->alloc[src_i];
     p.dbg_src_hi = e->alloc[src_i] + e->alloc_bytes;
@@ -412,6 +417,7 @@ std::vector<Pass> make_passes(const b2c_engine *e, int reps) {
             ps.k = ks[j];
             ps.group_end = j == n - 1;
             ps.check = ps.group_end && ce > 0 && done % ce == 0;
+            ps.interval = ce > 0 ? (unsigned)((done - 1) / ce + 1) : 0u;
             ps.iters_after = (unsigned)done;
             ps.ext = e->any_nb ? ext : 0;
             ps.mode = 0;
@@ -426,7 +432,18 @@ std::vector<Pass> make_passes(const b2c_engine *e, int reps) {
     return v;
 }
 
+// The stream of the passes joins the reduction of the check with this parity (if one is in flight).
+int join_check(b2c_engine *e, unsigned parity, cudaStream_t s) {
+    if (!e->check_pending[parity & 1u]) return B2C_OK;
+    CK(cudaStreamWaitEvent(s, e->ev_check[parity & 1u], 0));
+    e->check_pending[parity & 1u] = false;
+    return B2C_OK;
+}
+
 int enqueue_pass(b2c_engine *e, const Pass &ps, bool device_epoch, cudaStream_t s) {
+    // a pass of interval j obeys the checks up to j-2: the newest of them must have been reduced
+    // (the one before it was joined an interval ago); that also frees its parity's "changed" word
+    if (ps.interval >= 3 && join_check(e, ps.interval, s) != B2C_OK) return B2C_ECUDA;
     if (e->kernel == B2C_KERNEL_NAIVE) {
         if (e->any_nb) {  // the naive kernel reads the frame without looking at the flags
             unsigned mask = 0;
@@ -453,7 +470,7 @@ int enqueue_pass(b2c_engine *e, const Pass &ps, bool device_epoch, cudaStream_t 
         if (e->any_nb && (ps.mode & kHaloPush) && !p.halo.fused) {
             PushParams q;
             fill_push_params(e, e->cur ^ 1, device_epoch, q);
-            if (e->opts.check_every > 0) q.converged = e->pad + kPadConverged;
+            if (e->opts.check_every > 0) { q.converged = e->pad + kPadConverged; q.interval = ps.interval; }
             CK(launch_halo_push(q, s));
             e->launches++;
         }
@@ -461,8 +478,12 @@ int enqueue_pass(b2c_engine *e, const Pass &ps, bool device_epoch, cudaStream_t 
     e->cur ^= 1;
     if (e->any_nb && ps.group_end) e->epoch++;
     if (ps.check) {
+        // The reduction of this check runs on a side stream beside the next interval; the stream
+        // of the passes only joins it again in front of the interval after that (top of this
+        // function).  So the all-ranks handshake is off the critical path, and every rank still
+        // skips from exactly the same pass on (PassParams::interval).
         ConvergeParams c{};
-        c.changed = e->pad + kPadChanged;
+        c.changed = e->pad + kPadChanged + (ps.interval & 1u);
         c.slots = e->pad + kPadSlots;
         const int n = e->P * e->Q;
         for (int k = 0; k < n; ++k) c.peer_slots[k] = (n == 1 ? e->pad : e->rank_pad[k]) + kPadSlots;
@@ -472,13 +493,33 @@ int enqueue_pass(b2c_engine *e, const Pass &ps, bool device_epoch, cudaStream_t 
         c.converged = e->pad + kPadConverged;
         c.converged_at = e->pad + kPadConvergedAt;
         c.iters_after = ps.iters_after;
+        c.check_no = ps.interval;
+        cudaStream_t cs = s;
+        if (s) {   // not beside the legacy default stream: there the reduction stays in line
+            if (!e->side) {
+                CK(cudaStreamCreateWithFlags(&e->side, cudaStreamNonBlocking));
+                CK(cudaEventCreateWithFlags(&e->ev_fork, cudaEventDisableTiming));
+                CK(cudaEventCreateWithFlags(&e->ev_join, cudaEventDisableTiming));
+            }
+            if (!e->ev_check[0]) {
+                CK(cudaEventCreateWithFlags(&e->ev_check[0], cudaEventDisableTiming));
+                CK(cudaEventCreateWithFlags(&e->ev_check[1], cudaEventDisableTiming));
+            }
+            CK(cudaEventRecord(e->ev_fork, s));
+            CK(cudaStreamWaitEvent(e->side, e->ev_fork, 0));
+            cs = e->side;
+        }
         if (e->nvls_mc && n > 1) {
             NvlsParams nv{e->nvls_local, e->nvls_mc, n, e->rank};
-            CK(launch_converge_nvls(c, nv, s));
+            CK(launch_converge_nvls(c, nv, cs));
         } else {
-            CK(launch_converge(c, s));
+            CK(launch_converge(c, cs));
         }
         e->launches++;
+        if (s) {
+            CK(cudaEventRecord(e->ev_check[ps.interval & 1u], e->side));
+            e->check_pending[ps.interval & 1u] = true;
+        }
     }
     return B2C_OK;
 }
@@ -1014,6 +1055,7 @@ void b2c_engine_destroy(b2c_engine *e) {
     if (e->side) cudaStreamDestroy(e->side);
     if (e->ev_fork) cudaEventDestroy(e->ev_fork);
     if (e->ev_join) cudaEventDestroy(e->ev_join);
+    for (auto &ev : e->ev_check) if (ev) cudaEventDestroy(ev);
     for (void *p : e->ipc_opened) cudaIpcCloseMemHandle(p);
     if (e->tma) tma_destroy(e->tma);
     for (auto &b : e->res_xbuf) if (b) cudaFree(b);
@@ -1296,7 +1338,7 @@ int run_streaming(b2c_engine *e, int reps, cudaStream_t s) {
     // absolute epochs into the parameters.
     const bool device_epoch = e->opts.check_every == 0 && e->kernel != B2C_KERNEL_NAIVE;
     if (e->opts.check_every > 0) {
-        CK(cudaMemsetAsync(e->pad + kPadConverged, 0, 2 * sizeof(uint32_t), s));
+        CK(cudaMemsetAsync(e->pad + kPadChanged, 0, 4 * sizeof(uint32_t), s));   // changed[2], converged, converged_at
         e->last_passes = passes;
         e->run_epoch0 = e->epoch;
         e->run_cur0 = e->cur;
@@ -1360,6 +1402,7 @@ int run_streaming(b2c_engine *e, int reps, cudaStream_t s) {
     for (const Pass &ps : passes)
         if (rc != B2C_OK || (rc = enqueue_pass(e, ps, device_epoch, s)) != B2C_OK) return rc;
     if ((rc = courier_end(e, s)) != B2C_OK) return rc;
+    if (s && (join_check(e, 0, s) != B2C_OK || join_check(e, 1, s) != B2C_OK)) return B2C_ECUDA;   // reductions still in flight
     return enqueue_epoch_sync(e, device_epoch, s);
 }
 
@@ -1420,10 +1463,12 @@ int b2c_engine_iterations_done(b2c_engine *e) {
             // buffer index and epoch to the state right after the converging pass.
             int cur = e->run_cur0;
             uint32_t ep = e->run_epoch0;
+            // v[0] = number c of the check that found the fixed point: every rank ran the intervals up
+            // to c+1 and skipped the rest (the image did not change any more after check c)
             for (const Pass &ps : e->last_passes) {
+                if (ps.interval > v[0] + 1) break;
                 cur ^= 1;
                 if (e->any_nb && ps.group_end) ep++;
-                if (ps.iters_after >= v[1]) break;   // a check pass ends its group
             }
             e->cur = cur;
             e->epoch = e->epoch_dev = ep;
@@ -1524,14 +1569,28 @@ int b2c_debug_pass_plans(int rows, int cols, int channels, int has_neighbours, i
 
 static const int kTuneCand[] = {24, 32, 40, 48, 56, 64, 80, 96, 112, 128, 160, 192};
 
-static int tune_candidate(const b2c_engine *e, int i) {
+// Candidate i -> (strip bytes, rows per warp); returns the number of candidates for i < 0, 0 for an
+// index past the end.  Strip widths: the planned one first, then the other of {16, 8} unless the
+// caller fixed it (narrower strips never won on blocks large enough to be tuned).
+static int tune_candidate(const b2c_engine *e, int i, int *sb_out, int *cr_out) {
+    int sbs[2] = {e->SB0 > 0 ? e->SB0 : e->SB, 0};
+    int nsb = 1;
+    if (e->opts.strip_bytes == 0) {
+        const int other = sbs[0] == 16 ? 8 : 16;
+        if (e->K * (other / 4) <= 16) sbs[nsb++] = other;
+    }
     int n = 0;
     const int lo = min_edge_chunk(e, e->K);
-    for (int c : kTuneCand) {
-        if (c < lo || 2 * c > e->R) continue;
-        if (n == i) return c;
-        ++n;
-    }
+    for (int b = 0; b < nsb; ++b)
+        for (int c : kTuneCand) {
+            if (c < lo || 2 * c > e->R) continue;
+            if (n == i) {
+                if (sb_out) *sb_out = sbs[b];
+                if (cr_out) *cr_out = c;
+                return c;
+            }
+            ++n;
+        }
     return i < 0 ? n : 0;
 }
 
@@ -1541,19 +1600,27 @@ int b2c_engine_tune_count(const b2c_engine *e) {
     if (off || e->chunk_rows_fixed || e->P * e->Q == 1 || !e->any_nb) return 0;
     if (e->kernel != B2C_KERNEL_STREAM && e->kernel != B2C_KERNEL_TMA) return 0;
     if ((double)e->bw * e->R < 4e6) return 0;   // a pass is shorter than a handshake: keep the model
-    return tune_candidate(e, -1);
+    return tune_candidate(e, -1, nullptr, nullptr);
+}
+
+static void tune_apply(b2c_engine *e, int sb, int cr) {
+    e->SB = sb;
+    e->opts.chunk_rows = cr;
+    e->persist_ctas = 0;   // occupancy depends on the strip width
+    e->plan_cache.clear();
+    drop_graphs(e);
 }
 
 // Times candidate i with the halo exchange live: a fresh exchange, one untimed stretch, one timed
 // stretch of the iteration loop on whatever the buffers hold (kernel time does not depend on pixel
 // values).  Returns milliseconds on this rank; the caller reduces with MAX over the ranks.
 double b2c_engine_tune_time(b2c_engine *e, int i, void *stream) {
-    if (!e || tune_candidate(e, i) <= 0 || !e->connected) return -1.0;
+    int sb = 0, cr = 0;
+    if (!e || tune_candidate(e, i, &sb, &cr) <= 0 || !e->connected) return -1.0;
     if (cudaSetDevice(e->device) != cudaSuccess) return -1.0;
     cudaStream_t s = (cudaStream_t)stream;
-    e->opts.chunk_rows = tune_candidate(e, i);
-    e->plan_cache.clear();
-    drop_graphs(e);
+    if (e->SB0 == 0) e->SB0 = e->SB;
+    tune_apply(e, sb, cr);
     const int ug = e->opts.use_graph;
     e->opts.use_graph = 0;
     const int reps = 8 * std::max(e->F, e->K);
@@ -1574,9 +1641,10 @@ double b2c_engine_tune_time(b2c_engine *e, int i, void *stream) {
 
 int b2c_engine_tune_set(b2c_engine *e, int i) {
     if (!e) return B2C_EINVAL;
-    e->opts.chunk_rows = i >= 0 ? tune_candidate(e, i) : 0;   // 0 = the modelled plan
-    e->plan_cache.clear();
-    drop_graphs(e);
+    if (e->SB0 == 0) e->SB0 = e->SB;
+    int sb = e->SB0, cr = 0;   // i < 0: the modelled plan
+    if (i >= 0 && tune_candidate(e, i, &sb, &cr) <= 0) return B2C_EINVAL;
+    tune_apply(e, sb, cr);
     return B2C_OK;
 }
 

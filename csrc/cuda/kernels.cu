@@ -219,7 +219,10 @@ __global__ void halo_push_kernel(const PushParams q) {
     const int d = blockIdx.y;
     // After the convergence latch every pass is skipped on every rank; the ring pushes that
     // follow them must be skipped too or they would publish epochs nobody computed.
-    if (q.converged && *q.converged) return;
+    if (q.converged) {
+        const unsigned int c = *q.converged;
+        if (c != 0 && c + 1 < q.interval) return;
+    }
     const uint32_t base = q.epoch_base ? __ldcg(q.epoch_base) : 0u;
     if (q.epoch_word && blockIdx.x == 0 && d == 0 && threadIdx.x == 0) *q.epoch_word = q.post_epoch;
     if (!q.peer_dst[d]) return;
@@ -344,8 +347,9 @@ __global__ void converge_kernel(const ConvergeParams c) {
     }
     any = __any_sync(kFull, any != 0);
     if (lane == 0 && !any && !*c.converged) {
-        *c.converged = 1;
         *c.converged_at = c.iters_after;
+        __threadfence();
+        *c.converged = c.check_no;
     }
 }
 
@@ -418,8 +422,9 @@ __global__ void converge_nvls_kernel(const ConvergeParams c, const NvlsParams n)
     n.local[slot] = 0;
     __threadfence_system();
     if (!(v & 0xffffu) && !*c.converged) {
-        *c.converged = 1;
         *c.converged_at = c.iters_after;
+        __threadfence();
+        *c.converged = c.check_no;
     }
 }
 

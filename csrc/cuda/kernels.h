@@ -28,7 +28,8 @@ struct PushParams {
     int wait_epoch_valid;
     const uint32_t *epoch_base;      // device word holding the epoch at the start of the run (null: 0)
     uint32_t *epoch_word;            // when set, block (0,0) stores post_epoch there (initial exchange)
-    const unsigned int *converged;   // when set and non-zero the push is skipped (like the passes)
+    const unsigned int *converged;   // as PassParams::converged: the push is skipped like the passes of its interval
+    unsigned int interval;
 #ifdef B2C_DEBUG
     long long dbg_before, dbg_after; // bytes of an allocation before / after its interior origin
     int dbg_rank;
@@ -43,8 +44,9 @@ struct ConvergeParams {
     uint32_t *peer_slots[kMaxRanks];  // every rank's slot array (index = rank)
     int nranks, rank;
     unsigned int seq;             // check sequence number (>= 1)
-    unsigned int *converged;      // latched flag
+    unsigned int *converged;      // latched: number of the check (1-based within the run) that found the fixed point
     unsigned int *converged_at;   // iterations completed when it latched
+    unsigned int check_no;        // this check's number within the run
     unsigned int iters_after;
 };
 

@@ -94,7 +94,8 @@ struct alignas(16) PassParams {
     int hlo;             // window bytes left of the valid band
     int zero_n, zero_s, zero_w, zero_e;  // outside that side is outside the image (ZERO mode)
     unsigned int *changed;  // CHECK: OR-accumulated "last stage changed a byte"
-    const unsigned int *converged;  // when set (non-null and non-zero) the pass is skipped
+    const unsigned int *converged;  // check number at which the fixed point was detected (0: not yet), or null
+    unsigned int interval;          // check interval this pass belongs to (1-based); skipped iff *converged + 1 < interval
     int org_x, org_y;       // position of src/dst (0,0) inside the allocation (bytes, rows): TMA coordinates
     int raster;             // work order: 0 ring-first, 1 chunk-major, 2 ring-LAST (ring-first reversed)
 #ifdef B2C_DEBUG
@@ -630,7 +631,12 @@ __device__ __forceinline__ void stream_warp(const PassParams &p, const int wid, 
     // launches without the programmatic-serialization attribute.
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     asm volatile("griddepcontrol.wait;" ::: "memory");
-    if (p.converged && *p.converged) return;  // fixed point already reached: nothing changes any more
+    // Fixed point detected at check c: every rank runs interval c+1 to the end (the reduction of
+    // check c is still in flight on another stream meanwhile) and skips everything from c+2 on.
+    if (p.converged) {
+        const unsigned int c = *p.converged;
+        if (c != 0 && c + 1 < p.interval) return;
+    }
     stream_tile<K, NW, CH, CHECK>(p, band, chunk, lane, make_feed);
 }
 

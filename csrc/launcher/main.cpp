@@ -42,7 +42,7 @@ struct Shared {
     double phase_ms[kMaxWorkers][5];  // read, upload, loop, download, write
     int iterations[kMaxWorkers];
     char plan[kMaxWorkers][512];
-    double tune_ms[kMaxWorkers][16];      // coupled tuning: every rank's time per candidate
+    double tune_ms[kMaxWorkers][32];      // coupled tuning: every rank's time per candidate
     long long start_wait[kMaxWorkers];    // SM cycles each rank spent in the device-side start barrier
 };
 
@@ -145,7 +145,7 @@ int worker(const b2c_cli &cli, int rank, int n, int P, int Q, Shared *sh) {
         // the slowest rank's time decides (the buffers hold no image yet)
         const int nc = b2c_engine_tune_count(e);
         if (nc > 0) {
-            for (int i = 0; i < nc && i < 16; ++i) {
+            for (int i = 0; i < nc && i < 32; ++i) {
                 const double ms = b2c_engine_tune_time(e, i, s);
                 if (ms < 0) {
                     fprintf(stderr, "b200conv[%d]: %s\n", rank, b2c_last_error());
@@ -156,7 +156,7 @@ int worker(const b2c_cli &cli, int rank, int n, int P, int Q, Shared *sh) {
             if (!barrier(sh, n)) return 1;
             int best = 0;
             double best_ms = 1e300;
-            for (int i = 0; i < nc && i < 16; ++i) {
+            for (int i = 0; i < nc && i < 32; ++i) {
                 double worst = 0;
                 for (int k = 0; k < n; ++k) worst = sh->tune_ms[k][i] > worst ? sh->tune_ms[k][i] : worst;
                 if (worst < best_ms) { best_ms = worst; best = i; }
