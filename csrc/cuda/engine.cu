@@ -868,7 +868,7 @@ int autotune_chunk_rows(b2c_engine *e) {
             drop_graphs(e);
             // the path a real run takes (persistent kernel or one launch per pass), once to warm up
             // and build its tables, once timed
-            const int passes = bytes < 16e6 ? 40 : (bytes < 128e6 ? 8 : 3);   // short passes: average more of them
+            const int passes = bytes < 16e6 ? 40 : (bytes < 128e6 ? 8 : 6);   // short passes: average more of them
             int rr = run_streaming(e, passes * e->K, s);
             cudaEventRecord(ev0, s);
             if (rr == B2C_OK) rr = run_streaming(e, passes * e->K, s);
