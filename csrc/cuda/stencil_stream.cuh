@@ -640,8 +640,11 @@ __device__ __forceinline__ void stream_warp(const PassParams &p, const int wid, 
     stream_tile<K, NW, CH, CHECK>(p, band, chunk, lane, make_feed);
 }
 
+// The CHECK variants keep one more row of lanes (the last stage's input, to compare with its
+// output): under the 128-register cap that costs 400 bytes of spills inside the row loop, so they
+// trade a quarter of the occupancy for registers (one pass in five at check_every = 20).
 template <int K, int NW, int CH, bool CHECK>
-__global__ void __launch_bounds__(kWarpsPerCta * 32, B2C_MIN_CTAS)
+__global__ void __launch_bounds__(kWarpsPerCta * 32, (CHECK && K * NW >= 16) ? B2C_MIN_CTAS - 1 : B2C_MIN_CTAS)
 stream_kernel(const PassParams p) {
     const int lane = threadIdx.x & 31;
     const int wid = blockIdx.x * kWarpsPerCta + (threadIdx.x >> 5);
