@@ -381,6 +381,8 @@ def run_reference(a):
     import install_ref
 
     exe = ROOT / "baseline" / "_ref" / "cuda" / "cuda_convolution"
+    if os.environ.get("B200CONV_REF_EXE"):   # test hook (tests/test_bench_reference_arm.py): a stand-in binary
+        exe = Path(os.environ["B200CONV_REF_EXE"])
     try:
         if not exe.exists():
             install_ref.copy_tree()

@@ -34,3 +34,15 @@ def test_command_line():
     assert r.returncode == 0, r.stderr[-1500:]
     d = json.loads(r.stdout)
     assert d["grid"] == [2, 2] and d["block"] == [8192, 8192] and d["neighbour_gpus_per_rank"] == [3, 3, 3, 3]
+
+
+def test_streaming_plan_of_the_bench_shape_on_8_gpus():
+    s = plan(16384, 16384, 3, gpus=8, reps=1000)["streaming_plan"]
+    assert s["fused_iterations_per_pass"] == 4 and s["strip_bytes"] == 16 and s["bands"] == 26
+    assert s["halo_depth_iterations"] == 32 and s["passes_per_run"] == 250
+    assert s["halo_exchanges_per_run"] == 32                 # 31 groups of 32 iterations + one of 8
+    assert s["extra_rows_recomputed_per_side_max"] == 28     # first pass of a group: F - K rows into the frame
+    assert s["auto_kernel"].startswith("stream (") and s["host_launches_per_run"] == 2
+    one = plan(16384, 16384, 3, gpus=1, reps=1000)["streaming_plan"]
+    assert one["halo_exchanges_per_run"] == 0 and one["auto_kernel"].startswith("stream-persistent")
+    assert plan(1920, 2520, 1)["streaming_plan"]["auto_kernel"].startswith("resident")
