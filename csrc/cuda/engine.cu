@@ -838,6 +838,10 @@ int autotune_chunk_rows(b2c_engine *e) {
     e->any_nb = false;
     const int use_graph = e->opts.use_graph;
     e->opts.use_graph = 0;
+    // timed without the convergence check: on the all-zero buffers the first check would end the run,
+    // and its bookkeeping (a pending rewind of buffer index and epoch) has no business in a trial
+    const int check_every = e->opts.check_every;
+    e->opts.check_every = 0;
     cudaStream_t s = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     int rc = B2C_OK, best = 0;
@@ -892,6 +896,7 @@ int autotune_chunk_rows(b2c_engine *e) {
     e->any_nb = any_nb;
     e->opts.chunk_rows = best;   // 0 (model) when nothing was timed
     e->opts.use_graph = use_graph;
+    e->opts.check_every = check_every;
     e->plan_cache.clear();
     drop_graphs(e);
     e->cur = 0;
@@ -1621,8 +1626,9 @@ double b2c_engine_tune_time(b2c_engine *e, int i, void *stream) {
     cudaStream_t s = (cudaStream_t)stream;
     if (e->SB0 == 0) e->SB0 = e->SB;
     tune_apply(e, sb, cr);
-    const int ug = e->opts.use_graph;
+    const int ug = e->opts.use_graph, ce = e->opts.check_every;
     e->opts.use_graph = 0;
+    e->opts.check_every = 0;   // a trial is not a run: no early exit on whatever the buffers hold, no pending rewind
     const int reps = 8 * std::max(e->F, e->K);
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     float ms = -1.f;
@@ -1636,6 +1642,7 @@ double b2c_engine_tune_time(b2c_engine *e, int i, void *stream) {
     if (ev0) cudaEventDestroy(ev0);
     if (ev1) cudaEventDestroy(ev1);
     e->opts.use_graph = ug;
+    e->opts.check_every = ce;
     return ms;
 }
 
