@@ -1536,9 +1536,11 @@ int b2c_debug_band_plan(int rows, int cols, int channels, int has_neighbours, in
 }
 
 // Test hook (host only): the pass list of a run and each pass's plan, for the CPU property tests of
-// the grouped halo exchange.  Per pass 12 ints: {k, ext, mode, group_end, rows, row_bytes, nbands,
-// nchunks, chunk_rows, last_chunk_rows, nbw, nbe}.  Returns the number of passes (at most max_passes
-// are written) or a negative code.  A rank with neighbours on all eight sides is modelled.
+// the grouped halo exchange and of the persistent kernel's tile dependencies.  Per pass 16 ints:
+// {k, ext, mode, group_end, rows, row_bytes, nbands, nchunks, chunk_rows, last_chunk_rows, nbw, nbe,
+// hlo, vw, xn, xwb} (rows / row_bytes of the extended block; xn rows and xwb bytes of it lie in the
+// north / west frame).  Returns the number of passes (at most max_passes are written) or a negative
+// code.  A rank with neighbours on all eight sides is modelled.
 int b2c_debug_pass_plans(int rows, int cols, int channels, int has_neighbours, int tb, int strip_bytes, int chunk_rows,
                          int halo_depth, int reps, int sm_count, int *out, int max_passes) {
     if (rows <= 0 || cols <= 0 || (channels != 1 && channels != 3) || reps < 0 || !out) return B2C_EINVAL;
@@ -1561,9 +1563,10 @@ int b2c_debug_pass_plans(int rows, int cols, int channels, int has_neighbours, i
     for (const Pass &ps : passes) {
         if (n < max_passes) {
             const BandPlan bp = make_band_plan(&e, ps.k, ps.ext);
-            const int v[12] = {ps.k, ps.ext, ps.mode, ps.group_end ? 1 : 0, bp.rows, bp.bw, bp.nbands, bp.nchunks,
-                               bp.chunk_rows, bp.rows - (bp.nchunks - 1) * bp.chunk_rows, bp.nbw, bp.nbe};
-            memcpy(out + 12 * n, v, sizeof v);
+            const int v[16] = {ps.k, ps.ext, ps.mode, ps.group_end ? 1 : 0, bp.rows, bp.bw, bp.nbands, bp.nchunks,
+                               bp.chunk_rows, bp.rows - (bp.nchunks - 1) * bp.chunk_rows, bp.nbw, bp.nbe,
+                               bp.hlo, bp.vw, bp.xn, bp.xwb};
+            memcpy(out + 16 * n, v, sizeof v);
         }
         ++n;
     }

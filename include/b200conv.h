@@ -360,8 +360,8 @@ int b2c_debug_band_plan(int rows, int cols, int channels, int has_neighbours, in
                         int chunk_rows, int kernel, int sm_count, int out[10]);
 
 /* Test hook (host only): the passes of a `reps`-iteration run of a rank with eight neighbours and
- * the plan of each; 12 ints per pass {k, ext, mode, group_end, rows, row_bytes, nbands, nchunks,
- * chunk_rows, last_chunk_rows, nbw, nbe}.  Returns the number of passes. */
+ * the plan of each; 16 ints per pass {k, ext, mode, group_end, rows, row_bytes, nbands, nchunks,
+ * chunk_rows, last_chunk_rows, nbw, nbe, hlo, vw, xn, xwb}.  Returns the number of passes. */
 int b2c_debug_pass_plans(int rows, int cols, int channels, int has_neighbours, int tb, int strip_bytes,
                          int chunk_rows, int halo_depth, int reps, int sm_count, int *out, int max_passes);
 

@@ -43,10 +43,10 @@ def plan(width: int, height: int, channels: int, gpus: int = 1, reps: int = 1000
     # the streaming plan of one rank (host-side planner hooks of the C core; model plan, no timing)
     has_nb = multi or boundary == "torus"
     streaming = None
-    buf = (C.c_int * (12 * 4096))()
+    buf = (C.c_int * (16 * 4096))()
     n = lib.b2c_debug_pass_plans(rows, cols, channels, int(has_nb), 0, 0, 0, 0, int(reps), sms, buf, 4096)
     if n > 0:
-        passes = [list(buf[12 * i:12 * i + 12]) for i in range(min(n, 4096))]
+        passes = [list(buf[16 * i:16 * i + 16]) for i in range(min(n, 4096))]
         groups = sum(p[3] for p in passes) if has_nb else 0
         bp = (C.c_int * 10)()
         lib.b2c_debug_band_plan(rows, cols, channels, int(has_nb), 0, 0, 0, 0, sms, bp)

@@ -89,10 +89,10 @@ def test_pass_groups_of_a_rank_with_neighbours(rows, cols, ch, tb, strip, chunk,
     """One halo exchange per group of passes: what every pass of a group must satisfy so that the
     kernels' ring-membership rules (first/last chunk, first/last bands) cover every frame access."""
     WAIT_DATA, POST_ACK, WAIT_ACK, PUSH = 1, 2, 4, 8
-    buf = (C.c_int * (12 * 256))()
+    buf = (C.c_int * (16 * 256))()
     n = lib.b2c_debug_pass_plans(rows, cols, ch, 1, tb, strip, chunk, halo_depth, reps, 148, buf, 256)
     assert 0 < n <= 256
-    passes = [list(buf[12 * i:12 * i + 12]) for i in range(n)]
+    passes = [list(buf[16 * i:16 * i + 12]) for i in range(n)]
     out = (C.c_int * 10)()
     lib.b2c_debug_band_plan(rows, cols, ch, 1, tb, strip, chunk, 0, 148, out)
     bw = cols * ch
@@ -122,3 +122,54 @@ def test_pass_groups_of_a_rank_with_neighbours(rows, cols, ch, tb, strip, chunk,
                 assert not g[2] & PUSH
             group = []
     assert group == []
+
+
+# ---- the persistent kernel's tile dependencies (stencil_stream.cuh, stream_persist_kernel)
+
+def _tiles(ps, ch, win):
+    """Every (band, chunk) of a pass with the regions it needs to read and the region it writes, in
+    the coordinates of the un-extended block (rows, bytes)."""
+    k, ext, mode, gend, prow, pbw, nb, nc, cr, last, nbw, nbe, hlo, vw, xn, xwb = ps
+    out = {}
+    for c in range(nc):
+        r0, r1 = c * cr, (prow if c == nc - 1 else (c + 1) * cr)
+        for b in range(nb):
+            c0, c1 = b * vw, min((b + 1) * vw, pbw)
+            assert c0 - k * ch >= b * vw - hlo and c1 + k * ch <= b * vw - hlo + win      # the window holds what is needed
+            write = (r0 - xn, r1 - xn, c0 - xwb, c1 - xwb)
+            read = (r0 - k - xn, r1 + k - xn, c0 - k * ch - xwb, c1 + k * ch - xwb)
+            out[(b, c)] = (read, write)
+    return out
+
+
+def _overlap(a, b):
+    return a[0] < b[1] and b[0] < a[1] and a[2] < b[3] and b[2] < a[3]
+
+
+@settings(max_examples=120, deadline=None)
+@given(rows=st.integers(40, 700), cols=st.integers(40, 900), ch=st.sampled_from([1, 3]),
+       chunk=st.sampled_from([0, 9, 33, 64]), strip=st.sampled_from([0, 4, 8, 16]),
+       halo_depth=st.sampled_from([0, 8, 16, 32]), has_nb=st.booleans())
+def test_a_tile_waits_for_every_tile_it_depends_on(rows, cols, ch, chunk, strip, halo_depth, has_nb):
+    """A work item (pass t, band, chunk) of the persistent kernel waits for the 3x3 neighbourhood
+    (clamped) of pass t-1 in THAT pass's tiling.  With neighbours the block is extended into the
+    frame by a different amount from pass to pass, so the two tilings are shifted against each other
+    and may differ by one band / chunk.  Every tile of pass t-1 that wrote what the item reads (RAW),
+    or read what the item overwrites (WAR: pass t writes the buffer pass t-1 read), must be in that
+    set — checked on the real geometry of the plan."""
+    buf = (C.c_int * (16 * 64))()
+    n = lib.b2c_debug_pass_plans(rows, cols, ch, int(has_nb), 4, strip, chunk, halo_depth, 48, 148, buf, 64)
+    assert 0 < n <= 64
+    passes = [list(buf[16 * i:16 * i + 16]) for i in range(n)]
+    passes = [p for p in passes if p[0] == 4]          # the table of the persistent kernel: passes with k == K
+    out = (C.c_int * 10)()
+    lib.b2c_debug_band_plan(rows, cols, ch, int(has_nb), 4, strip, chunk, 0, 148, out)
+    win = 32 * out[8]
+    for prev, cur in zip(passes, passes[1:]):
+        tp, tc = _tiles(prev, ch, win), _tiles(cur, ch, win)
+        pnb, pnc = prev[6], prev[7]
+        for (b, c), (read, write) in tc.items():
+            waits = {(min(max(b + db, 0), pnb - 1), min(max(c + dc, 0), pnc - 1)) for db in (-1, 0, 1) for dc in (-1, 0, 1)}
+            for key, (pread, pwrite) in tp.items():
+                if _overlap(pwrite, read) or _overlap(pread, write):
+                    assert key in waits, (prev, cur, (b, c), key)
