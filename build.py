@@ -32,7 +32,7 @@ NVCC_FLAGS = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "-Xcompil
               "-Xptxas", "-v", "--expt-relaxed-constexpr"] + ARCH + INCLUDES
 
 CORE_SOURCES = [
-    "csrc/core/decomp.cpp", "csrc/core/cli.cpp", "csrc/core/rawio.cpp", "csrc/core/oracle.cpp", "csrc/core/halo_emul.cpp", "csrc/core/resident_emul.cpp",
+    "csrc/core/decomp.cpp", "csrc/core/cli.cpp", "csrc/core/rawio.cpp", "csrc/core/oracle.cpp", "csrc/core/halo_emul.cpp", "csrc/core/resident_emul.cpp", "csrc/core/persist_emul.cpp",
     "csrc/cuda/kernels.cu", "csrc/cuda/stencil_tma.cu", "csrc/cuda/stencil_resident.cu", "csrc/cuda/engine.cu", "csrc/cuda/program.cu",
 ]
 

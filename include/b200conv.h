@@ -186,6 +186,15 @@ int b2c_emulate_resident_threads(const uint8_t *in, uint8_t *out, int width, int
                                  int repetitions, int boundary, int k, int sms, int max_delay_us,
                                  unsigned seed);
 
+/* Threaded host model of the persistent dataflow kernel's scheduling (one rank, ZERO boundary): a
+ * queue of (pass, chunk, band) items pulled by `workers` threads, per-tile "passes completed" words,
+ * an item starts when the 3x3 neighbourhood of the pass before is done, no barrier between passes.
+ * reps must be a multiple of k; vw = valid bytes per band; B2C_ETIMEOUT on a deadlock.  No
+ * counterpart in the reference. */
+int b2c_emulate_persist_threads(const uint8_t *in, uint8_t *out, int width, int height, int channels,
+                                int repetitions, int k, int vw, int chunk_rows, int workers, int max_delay_us,
+                                unsigned seed);
+
 /* --------------------------------------------------------------- GPU engine */
 
 typedef struct b2c_opts {

@@ -113,6 +113,7 @@ def _load() -> C.CDLL:
         "b2c_resident_plan": (I, [I, I, I, I, I, C.POINTER(I)]),
         "b2c_debug_map_work": (I, [I, I, I, I, I, C.POINTER(I), C.POINTER(I)]),
         "b2c_debug_band_plan": (I, [I, I, I, I, I, I, I, I, I, C.POINTER(I)]),
+        "b2c_emulate_persist_threads": (I, [u8p, u8p, I, I, I, I, I, I, I, I, I, C.c_uint]),
         "b2c_emulate_resident_threads": (I, [u8p, u8p, I, I, I, I, I, I, I, I, C.c_uint]),
         "b2c_engine_describe": (I, [P, C.c_char_p, C.c_size_t]),
         "b2c_engine_set_delay": (I, [P, L]),

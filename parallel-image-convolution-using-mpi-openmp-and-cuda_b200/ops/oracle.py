@@ -98,6 +98,17 @@ def threaded_resident_model(img, reps: int, boundary: str = "zero", k: int = 4, 
     return restore(out)
 
 
+def threaded_persist_model(img, reps: int, k: int = 4, vw: int = 480, chunk_rows: int = 32, workers: int = 8,
+                           max_delay_us: int = 0, seed: int = 0):
+    """Host model of the persistent kernel's work queue and tile dependencies (csrc/core/persist_emul.cpp)."""
+    flat, w, h, ch, restore = _as_image(img)
+    out = np.empty_like(flat)
+    check(lib.b2c_emulate_persist_threads(flat.ctypes.data, out.ctypes.data, w, h, ch, int(reps), int(k), int(vw),
+                                          int(chunk_rows), int(workers), int(max_delay_us), int(seed)),
+          "emulate_persist_threads")
+    return restore(out)
+
+
 def numpy_oracle(img, reps: int, boundary: str = "zero"):
     """Gaussian only.  Vectorised shifts on a padded int32 array; exact."""
     flat, w, h, ch, restore = _as_image(img)

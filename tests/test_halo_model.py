@@ -14,7 +14,7 @@ import numpy as np
 import pytest
 
 from b200conv import B2CError, reference_oracle
-from b200conv.ops import threaded_halo_model, threaded_resident_model
+from b200conv.ops import threaded_halo_model, threaded_persist_model, threaded_resident_model
 
 ROOT = Path(__file__).resolve().parent.parent
 
@@ -117,6 +117,22 @@ def test_resident_cta_protocol_model(case):
     assert (got == reference_oracle(img, reps, boundary)).all()
 
 
+@pytest.mark.parametrize("case", [
+    # (H, W, ch, reps, k, vw, chunk_rows, workers)
+    (96, 200, 1, 24, 4, 40, 8, 3),      # 5 bands x 12 chunks, far fewer workers than tiles
+    (61, 90, 3, 16, 4, 60, 7, 16),      # ragged last band and last chunk, more workers than a chunk row
+    (40, 64, 1, 32, 8, 64, 40, 4),      # one tile per pass: a pure chain
+    (130, 48, 3, 12, 2, 30, 5, 32),     # many thin tiles, workers spread over several passes at once
+])
+def test_persistent_kernel_queue_model(case):
+    # work items pulled from one counter, an item waits for the 3x3 neighbourhood of the pass before,
+    # no barrier between passes, random delays
+    h, w, ch, reps, k, vw, cr, workers = case
+    img = rnd(h, w, ch, seed=21)
+    got = threaded_persist_model(img, reps, k=k, vw=vw, chunk_rows=cr, workers=workers, max_delay_us=150, seed=7)
+    assert (got == reference_oracle(img, reps, "zero")).all()
+
+
 TSAN_MAIN = r"""
 #include <cstdio>
 #include <cstdlib>
@@ -182,6 +198,17 @@ int main() {
         int rc = b2c_emulate_resident_threads(in.data(), got.data(), RW_, RH_, 1, reps2, boundary, 4, 148, 100, 5);
         bad += rc != B2C_OK || memcmp(want.data(), got.data(), got.size()) != 0;
     }
+    {   // work queue + tile dependencies of the persistent kernel: 5 x 12 tiles per pass, 3 workers, then 16
+        const int PW = 200, PH = 96, preps = 24;
+        std::vector<uint8_t> in((size_t)PW * PH), want(in.size()), got(in.size());
+        srand(13);
+        for (auto &b : in) b = (uint8_t)rand();
+        b2c_oracle_blur(in.data(), want.data(), PW, PH, 1, preps, B2C_ZERO, B2C_GAUSSIAN);
+        for (int workers = 3; workers <= 16; workers += 13) {
+            int rc = b2c_emulate_persist_threads(in.data(), got.data(), PW, PH, 1, preps, 4, 40, 8, workers, 100, 3);
+            bad += rc != B2C_OK || memcmp(want.data(), got.data(), got.size()) != 0;
+        }
+    }
     printf("bad=%d\n", bad);
     return bad != 0;
 }
@@ -193,7 +220,8 @@ def test_model_is_race_free_under_thread_sanitizer(tmp_path):
     main = tmp_path / "main.cpp"
     main.write_text(TSAN_MAIN)
     exe = tmp_path / "halo_tsan"
-    srcs = [str(ROOT / "csrc/core" / f) for f in ("halo_emul.cpp", "resident_emul.cpp", "oracle.cpp", "decomp.cpp")]
+    srcs = [str(ROOT / "csrc/core" / f) for f in ("halo_emul.cpp", "resident_emul.cpp", "persist_emul.cpp", "oracle.cpp",
+                                                  "decomp.cpp")]
     cmd = ["g++", "-std=c++17", "-O1", "-g", "-fsanitize=thread", "-pthread", "-I", str(ROOT / "include"),
            "-I", str(ROOT / "csrc/core"), str(main), *srcs, "-o", str(exe)]
     b = subprocess.run(cmd, capture_output=True, text=True)
