@@ -40,6 +40,7 @@ bool apply_option(b2c_cli *c, const char *name, const char *val) {
     if (!strcmp(name, "tb")) return (c->tb = atoi(val)) >= 0;
     if (!strcmp(name, "kernel")) return (c->kernel = parse_kernel(val)) >= 0;
     if (!strcmp(name, "check-every")) return (c->check_every = atoi(val)) >= 0;
+    if (!strcmp(name, "halo-depth")) return (c->halo_depth = atoi(val)) >= 0;
     if (!strcmp(name, "checkpoint-every")) return (c->checkpoint_every = atoi(val)) >= 0;
     if (!strcmp(name, "json")) { c->json = val; return true; }
     if (!strcmp(name, "cpu")) {   // host fallback: thread count, or "all"
@@ -55,7 +56,7 @@ void apply_env(b2c_cli *c) {
         {"B200CONV_FILTER", "filter"},       {"B200CONV_TB", "tb"},
         {"B200CONV_KERNEL", "kernel"},       {"B200CONV_CHECK_EVERY", "check-every"},
         {"B200CONV_CHECKPOINT_EVERY", "checkpoint-every"}, {"B200CONV_JSON", "json"},
-        {"B200CONV_CPU", "cpu"}};
+        {"B200CONV_CPU", "cpu"},             {"B200CONV_HALO_DEPTH", "halo-depth"}};
     for (auto &n : names) {
         const char *v = getenv(n[0]);
         if (v && *v) apply_option(c, n[1], v);

@@ -115,6 +115,7 @@ int worker(const b2c_cli &cli, int rank, int n, int P, int Q, Shared *sh) {
     o.kernel = cli.kernel;
     o.tb = cli.tb;
     o.check_every = cli.check_every;
+    o.halo_depth = cli.halo_depth;
     WCK(cudaSetDevice(rank));
     b2c_engine *e = b2c_engine_create(rank, W, H, CH, P, Q, rank, &o);
     if (!e) {

@@ -97,6 +97,7 @@ typedef struct b2c_cli {
     int profile;        /* per-phase timings on stderr */
     const char *json;   /* path for the JSON report, NULL = none */
     int cpu;            /* --cpu N|all: run on N host threads (-1 = all cores) instead of GPUs; 0 = GPUs */
+    int halo_depth;     /* --halo-depth N: iterations between two halo exchanges (several GPUs / torus), 0 = auto */
 } b2c_cli;
 
 /* Grammar of Usage() mpi/mpi_convolution.c:328-348 and Initialization()

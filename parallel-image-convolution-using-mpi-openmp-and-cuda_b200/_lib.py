@@ -46,7 +46,7 @@ class Cli(C.Structure):
     _fields_ = [("image", C.c_char_p), ("width", C.c_int), ("height", C.c_int), ("repetitions", C.c_int),
                 ("channels", C.c_int), ("gpus", C.c_int), ("boundary", C.c_int), ("filter", C.c_int),
                 ("tb", C.c_int), ("kernel", C.c_int), ("check_every", C.c_int), ("checkpoint_every", C.c_int),
-                ("profile", C.c_int), ("json", C.c_char_p), ("cpu", C.c_int)]
+                ("profile", C.c_int), ("json", C.c_char_p), ("cpu", C.c_int), ("halo_depth", C.c_int)]
 
 
 class B2CError(RuntimeError):

@@ -35,6 +35,11 @@ def test_cli_extensions_and_env(monkeypatch):
     monkeypatch.setenv("B200CONV_TB", "2")
     d = parse_cli(["p", "x.raw", "8", "8", "2", "grey", "--tb", "4"])
     assert d["boundary"] == 1 and d["tb"] == 4  # flag beats env
+    assert d["halo_depth"] == 0                 # auto
+    monkeypatch.setenv("B200CONV_HALO_DEPTH", "8")
+    assert parse_cli(["p", "x.raw", "8", "8", "2", "grey"])["halo_depth"] == 8
+    assert parse_cli(["p", "x.raw", "8", "8", "2", "grey", "--halo-depth", "16"])["halo_depth"] == 16
+    assert parse_cli(["p", "x.raw", "8", "8", "2", "grey", "--halo-depth", "-1"]) is None
 
 
 def test_usage_text_matches_reference_wording():
