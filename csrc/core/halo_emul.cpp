@@ -23,6 +23,12 @@
 //     flight on a side stream meanwhile — the image is a fixed point, so nothing changes) and
 //     skips everything from interval c+2 on.
 //
+//   * optionally (`courier`) a rank does not store epochs into its neighbours itself: it release-stores
+//     them into words of its own, and a second thread per rank — the courier warp of the GPU engine,
+//     which keeps the system-scope fence out of the passes — acquires them and release-stores them
+//     into the neighbours.  The frames are then ordered through two hops (rank -> courier ->
+//     neighbour), which is exactly the cumulativity the GPU version relies on.
+//
 // Random sleeps can be injected at every point where the GPU ranks may drift apart.  Built with
 // -fsanitize=thread (tests/test_halo_model.py) the model shows that the protocol has no data race
 // on the frames; with `single_slot_set` it reproduces the lost-tag hang that the parity fixes.
@@ -47,6 +53,8 @@ struct Rank {
     int nb[8];
     std::atomic<uint32_t> flag[8];
     std::atomic<uint32_t> ack[8];
+    std::atomic<uint32_t> ready[16];     // courier mode: epochs handed over (0-7 data, 8-15 ack)
+    std::atomic<bool> finished{false};   // courier mode: the rank thread has published its last epoch
     std::unique_ptr<std::atomic<uint32_t>[]> slots;  // 2 sets x n ranks
     int iters = 0;
 };
@@ -138,17 +146,52 @@ struct World {
 
     void publish(int q, uint32_t epoch) {
         Rank &me = ranks[q];
-        for (int d = 0; d < 8; ++d)
-            if (me.nb[d] >= 0) ranks[me.nb[d]].flag[b2c::opposite_dir(d)].store(epoch, std::memory_order_release);
+        for (int d = 0; d < 8; ++d) {
+            if (me.nb[d] < 0) continue;
+            if (o.courier) me.ready[d].store(epoch, std::memory_order_release);
+            else ranks[me.nb[d]].flag[b2c::opposite_dir(d)].store(epoch, std::memory_order_release);
+        }
     }
 
     void publish_ack(int q, uint32_t epoch) {
         Rank &me = ranks[q];
-        for (int d = 0; d < 8; ++d)
-            if (me.nb[d] >= 0) ranks[me.nb[d]].ack[b2c::opposite_dir(d)].store(epoch, std::memory_order_release);
+        for (int d = 0; d < 8; ++d) {
+            if (me.nb[d] < 0) continue;
+            if (o.courier) me.ready[8 + d].store(epoch, std::memory_order_release);
+            else ranks[me.nb[d]].ack[b2c::opposite_dir(d)].store(epoch, std::memory_order_release);
+        }
+    }
+
+    // The courier of rank q: forwards whatever appears in the rank's `ready` words to the neighbours
+    // until the rank thread has finished and everything has been forwarded.
+    void run_courier(int q) {
+        Rank &me = ranks[q];
+        std::mt19937 rng(o.seed * 104729u + (unsigned)q);
+        uint32_t sent[16] = {0};
+        for (;;) {
+            const bool last_look = me.finished.load(std::memory_order_acquire);
+            for (int i = 0; i < 16; ++i) {
+                const int d = i & 7;
+                if (me.nb[d] < 0) continue;
+                const uint32_t v = me.ready[i].load(std::memory_order_acquire);
+                if (v == sent[i]) continue;
+                if (o.max_delay_us > 0)   // the system-scope publication can be slow (PCIe traffic)
+                    std::this_thread::sleep_for(std::chrono::microseconds(rng() % (unsigned)(o.max_delay_us + 1)));
+                Rank &peer = ranks[me.nb[d]];
+                (i < 8 ? peer.flag : peer.ack)[b2c::opposite_dir(d)].store(v, std::memory_order_release);
+                sent[i] = v;
+            }
+            if (last_look || failed.load(std::memory_order_relaxed)) return;
+            std::this_thread::yield();
+        }
     }
 
     void run_rank(int q, const uint8_t *in, uint8_t *out) {
+        run_rank_body(q, in, out);
+        ranks[q].finished.store(true, std::memory_order_release);   // the courier takes one last look and leaves
+    }
+
+    void run_rank_body(int q, const uint8_t *in, uint8_t *out) {
         Rank &me = ranks[q];
         std::mt19937 rng(o.seed * 7919u + (unsigned)q);
         auto jitter = [&] {
@@ -301,12 +344,15 @@ extern "C" int b2c_emulate_halo_threads(const uint8_t *in, uint8_t *out, int W, 
         b2c_neighbours(q, P, Q, boundary, r.nb);
         for (auto &f : r.flag) f.store(0);
         for (auto &f : r.ack) f.store(0);
+        for (auto &f : r.ready) f.store(0);
         r.slots.reset(new std::atomic<uint32_t>[2 * (size_t)w.n]);
         for (int k = 0; k < 2 * w.n; ++k) r.slots[k].store(0);
     }
     w.deadline = Clock::now() + std::chrono::milliseconds(opts->timeout_ms > 0 ? opts->timeout_ms : 20000);
     std::vector<std::thread> th;
     for (int q = 0; q < w.n; ++q) th.emplace_back([&w, q, in, out] { w.run_rank(q, in, out); });
+    if (opts->courier)
+        for (int q = 0; q < w.n; ++q) th.emplace_back([&w, q] { w.run_courier(q); });
     for (auto &t : th) t.join();
     if (w.failed.load()) {
         b2c::set_error("emulate_halo_threads: a rank waited past the deadline (protocol deadlock)");

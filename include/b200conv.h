@@ -161,6 +161,8 @@ typedef struct b2c_emul_opts {
     int images;          /* > 1: that many images back to back through the same buffers with no */
                          /*   barrier in between (image j = input XOR 37*j); needs check_every 0 */
     int halo_depth;      /* iterations between two halo exchanges (multiple of tb, <= 32); 0 = tb  */
+    int courier;         /* 1 = epochs reach the neighbours through a second thread per rank (the   */
+                         /*   courier warp of the GPU engine) instead of directly                   */
 } b2c_emul_opts;
 
 /* Returns B2C_OK (out = the gathered result of every image, max(1, images) x H x W*CH bytes;

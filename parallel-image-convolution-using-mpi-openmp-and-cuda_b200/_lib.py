@@ -39,7 +39,7 @@ class Opts(C.Structure):
 class EmulOpts(C.Structure):
     _fields_ = [("tb", C.c_int), ("check_every", C.c_int), ("max_delay_us", C.c_int), ("seed", C.c_uint),
                 ("timeout_ms", C.c_int), ("single_slot_set", C.c_int), ("stall_rank", C.c_int), ("stall_ms", C.c_int), ("images", C.c_int),
-                ("halo_depth", C.c_int)]
+                ("halo_depth", C.c_int), ("courier", C.c_int)]
 
 
 class Cli(C.Structure):

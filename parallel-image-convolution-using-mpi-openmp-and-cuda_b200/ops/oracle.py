@@ -70,7 +70,8 @@ def sharded_oracle(img, reps: int, grid, boundary: str = "zero", tb: int = 1):
 
 def threaded_halo_model(img, reps: int, grid, boundary: str = "zero", tb: int = 1, check_every: int = 0,
                         max_delay_us: int = 0, seed: int = 0, timeout_ms: int = 0, single_slot_set: bool = False,
-                        stall_rank: int = -1, stall_ms: int = 0, images: int = 1, halo_depth: int = 0):
+                        stall_rank: int = -1, stall_ms: int = 0, images: int = 1, halo_depth: int = 0,
+                        courier: bool = False):
     """-> (image, iterations run); with ``images`` > 1 a list of results (image j = input XOR 37*j, pushed
     through the same buffers back to back with no barrier in between, like ``ShardedPipeline``).
     Raises B2CError (code B2C_ETIMEOUT) when a rank deadlocks."""
@@ -78,7 +79,8 @@ def threaded_halo_model(img, reps: int, grid, boundary: str = "zero", tb: int = 
     n = max(1, int(images))
     out = np.empty((n,) + flat.shape, dtype=np.uint8)
     o = _lib.EmulOpts(int(tb), int(check_every), int(max_delay_us), int(seed), int(timeout_ms),
-                      int(bool(single_slot_set)), int(stall_rank), int(stall_ms), int(images), int(halo_depth))
+                      int(bool(single_slot_set)), int(stall_rank), int(stall_ms), int(images), int(halo_depth),
+                      int(bool(courier)))
     iters = C.c_int(0)
     check(lib.b2c_emulate_halo_threads(flat.ctypes.data, out.ctypes.data, w, h, ch, int(reps), BOUNDARY[boundary],
                                        int(grid[0]), int(grid[1]), C.byref(o), C.byref(iters)),

@@ -66,6 +66,18 @@ def test_one_exchange_per_group_of_passes(grid, boundary, tb, halo_depth, reps):
     assert (out == reference_oracle(img, reps, boundary)).all(), (grid, boundary, tb, halo_depth, reps)
 
 
+@pytest.mark.parametrize("grid,boundary,halo_depth,reps", [((2, 2), "zero", 0, 23), ((2, 4), "torus", 8, 37),
+                                                          ((1, 2), "torus", 16, 50), ((3, 3), "zero", 12, 30)])
+def test_epochs_forwarded_by_a_courier_thread(grid, boundary, halo_depth, reps):
+    # the rank hands its epochs to a second thread that publishes them to the neighbours (with its own
+    # random delay): frames are ordered through two hops, images back to back included
+    img = rnd(48, 48, 3, seed=14)
+    outs, _ = threaded_halo_model(img, reps, grid, boundary, tb=4, halo_depth=halo_depth, max_delay_us=200, seed=3,
+                                  images=3, courier=True)
+    for j, out in enumerate(outs):
+        assert (out == reference_oracle(img ^ np.uint8((37 * j) & 255), reps, boundary)).all(), j
+
+
 def test_grouped_exchange_with_images_back_to_back_and_with_checks():
     img = rnd(32, 64, 1, seed=13)
     outs, _ = threaded_halo_model(img, 19, (2, 4), "torus", tb=4, halo_depth=8, max_delay_us=300, seed=2, images=4)
@@ -180,6 +192,7 @@ int main() {
             b2c_emul_opts o;
             memset(&o, 0, sizeof o);
             o.tb = 4, o.max_delay_us = 50, o.seed = 5, o.stall_rank = -1, o.halo_depth = hd, o.images = 3;
+            o.courier = hd != 12;   // two of the three depths through courier threads
             int iters = 0;
             int rc = b2c_emulate_halo_threads(in.data(), many.data(), W2, H2, ch, reps2, boundary, 2, 4, &o, &iters);
             bad += rc != B2C_OK;
