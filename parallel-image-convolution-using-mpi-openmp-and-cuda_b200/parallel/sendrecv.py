@@ -4,7 +4,10 @@
 (mpi/mpi_convolution.c:156-240) onto ``torch.distributed``, with the missing corner exchange
 added so that the result is exact on every grid.  Per iteration: pack the four edge rows/columns
 and four corners (torch slicing), one grouped ``batch_isend_irecv``, unpack into the 1-pixel halo of
-a padded tensor, then one plain stencil pass over the block.
+a padded tensor, then one plain stencil pass over the block.  With ``halo_depth`` F > 1 the halo is
+F pixels deep and exchanged once per F iterations; in between, a rank recomputes the part of the
+halo that is still valid itself (its block extended by F-1, F-2, ... pixels towards the sides that
+have a neighbour) — the communication-avoiding schedule of the fused GPU engine, with messages.
 
 * backend ``nccl`` (``NcclHaloBlur``): CUDA tensors, ncclGroupStart + ncclSend/ncclRecv, byte-per-thread
   kernel ``b2c_stencil_step_device`` — the NCCL baseline that the fused peer-memory engine is
@@ -27,7 +30,7 @@ _OPP = {"N": "S", "S": "N", "W": "E", "E": "W", "NW": "SE", "SE": "NW", "NE": "S
 
 
 class SendRecvHaloBlur:
-    def __init__(self, width, height, channels, boundary="zero", group=None, device=None, threads=0):
+    def __init__(self, width, height, channels, boundary="zero", group=None, device=None, threads=0, halo_depth=1):
         self.group = group
         self.threads = int(threads)   # CPU only: threads per rank for the stencil pass (0 = all cores)
         self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
@@ -36,31 +39,36 @@ class SendRecvHaloBlur:
         self.nb = neighbours(self.rank, self.grid, boundary)
         self.r0, self.c0, self.R, self.C = block_of(self.rank, self.grid, height, width)
         self.bw = self.C * self.ch
-        pitch = (self.bw + 2 * self.ch + 127) // 128 * 128
+        # halo depth F: a halo pixel must come from the adjacent rank only
+        self.F = max(1, min(int(halo_depth), self.R, self.C))
+        self.fb = self.F * self.ch
+        pitch = (self.bw + 2 * self.fb + 127) // 128 * 128
         if device is None:
             device = "cuda" if dist.get_backend(group) == "nccl" else "cpu"
         dev = torch.device("cuda", torch.cuda.current_device()) if str(device).startswith("cuda") else torch.device("cpu")
-        self.buf = [torch.zeros((self.R + 2, pitch), dtype=torch.uint8, device=dev) for _ in range(2)]
+        self.buf = [torch.zeros((self.R + 2 * self.F, pitch), dtype=torch.uint8, device=dev) for _ in range(2)]
         self.cur = 0
+        self.exchanges = 0
 
     def _region(self, t, d, halo):
-        """Slice of the padded buffer: the edge we send towards d (halo=False) or the halo we
-        receive from d (halo=True)."""
-        ch, R, bw = self.ch, self.R, self.bw
+        """Slice of the padded buffer: the F-deep edge we send towards d (halo=False) or the F-deep halo
+        we receive from d (halo=True)."""
+        R, bw, F, fb = self.R, self.bw, self.F, self.fb
         dr, dc = _DIRS[d]
         if halo:
-            rows = slice(0, 1) if dr < 0 else (slice(R + 1, R + 2) if dr > 0 else slice(1, R + 1))
-            cols = slice(0, ch) if dc < 0 else (slice(ch + bw, 2 * ch + bw) if dc > 0 else slice(ch, ch + bw))
+            rows = slice(0, F) if dr < 0 else (slice(R + F, R + 2 * F) if dr > 0 else slice(F, R + F))
+            cols = slice(0, fb) if dc < 0 else (slice(fb + bw, 2 * fb + bw) if dc > 0 else slice(fb, fb + bw))
         else:
-            rows = slice(1, 2) if dr < 0 else (slice(R, R + 1) if dr > 0 else slice(1, R + 1))
-            cols = slice(ch, 2 * ch) if dc < 0 else (slice(bw, bw + ch) if dc > 0 else slice(ch, ch + bw))
+            rows = slice(F, 2 * F) if dr < 0 else (slice(R, R + F) if dr > 0 else slice(F, R + F))
+            cols = slice(fb, 2 * fb) if dc < 0 else (slice(bw, bw + fb) if dc > 0 else slice(fb, fb + bw))
         return t[rows, cols]
 
     def load(self, block: torch.Tensor):
-        self.buf[self.cur][1:self.R + 1, self.ch:self.ch + self.bw] = block.reshape(self.R, self.bw).to(self.buf[0].device)
+        self.buf[self.cur][self.F:self.R + self.F, self.fb:self.fb + self.bw] = \
+            block.reshape(self.R, self.bw).to(self.buf[0].device)
 
     def store(self) -> torch.Tensor:
-        out = self.buf[self.cur][1:self.R + 1, self.ch:self.ch + self.bw].contiguous()
+        out = self.buf[self.cur][self.F:self.R + self.F, self.fb:self.fb + self.bw].contiguous()
         return out if self.ch == 1 else out.reshape(self.R, self.C, self.ch)
 
     def exchange(self):
@@ -88,23 +96,37 @@ class SendRecvHaloBlur:
                 w.wait()
         for d, recv in recvs:
             self._region(src, d, True).copy_(recv)                                # unpack
+        self.exchanges += 1
 
     def run(self, repetitions: int):
-        for _ in range(int(repetitions)):
-            self.exchange()
-            stencil_step(self.buf[self.cur], self.buf[self.cur ^ 1], self.R, self.bw, self.ch, threads=self.threads)
-            self.cur ^= 1
+        left = int(repetitions)
+        F, fb, ch, R, bw = self.F, self.fb, self.ch, self.R, self.bw
+        has = {d: self.nb[d] >= 0 for d in ("N", "S", "W", "E")}
+        while left > 0:
+            g = min(F, left)
+            self.exchange()                      # one F-deep exchange per group of up to F iterations
+            for j in range(g):
+                ext = g - 1 - j                  # iterations left in the group: how far the block is extended
+                xn, xs = (ext if has["N"] else 0), (ext if has["S"] else 0)
+                xw, xe = (ext * ch if has["W"] else 0), (ext * ch if has["E"] else 0)
+                rows, row_bytes = R + xn + xs, bw + xw + xe
+                r0, c0 = F - xn - 1, fb - xw - ch   # view whose [1, ch] element is the first pixel computed
+                src = self.buf[self.cur][r0:r0 + rows + 2, c0:]
+                dst = self.buf[self.cur ^ 1][r0:r0 + rows + 2, c0:]
+                stencil_step(src, dst, rows, row_bytes, ch, threads=self.threads)
+                self.cur ^= 1
+            left -= g
 
 
 class NcclHaloBlur(SendRecvHaloBlur):
     """CUDA tensors over NCCL send/recv: the baseline arm of the multi-GPU benches."""
 
-    def __init__(self, width, height, channels, boundary="zero", group=None):
-        super().__init__(width, height, channels, boundary, group, device="cuda")
+    def __init__(self, width, height, channels, boundary="zero", group=None, halo_depth=1):
+        super().__init__(width, height, channels, boundary, group, device="cuda", halo_depth=halo_depth)
 
 
 class GlooHaloBlur(SendRecvHaloBlur):
     """CPU tensors over gloo, ``threads`` stencil threads per rank: the host-only arm."""
 
-    def __init__(self, width, height, channels, boundary="zero", group=None, threads=0):
-        super().__init__(width, height, channels, boundary, group, device="cpu", threads=threads)
+    def __init__(self, width, height, channels, boundary="zero", group=None, threads=0, halo_depth=1):
+        super().__init__(width, height, channels, boundary, group, device="cpu", threads=threads, halo_depth=halo_depth)

@@ -28,13 +28,14 @@ def main():
     ap.add_argument("--color", default="rgb", choices=["grey", "rgb"])
     ap.add_argument("--reps", type=int, default=40)
     ap.add_argument("--threads", type=int, default=2)
+    ap.add_argument("--halo-depth", type=int, default=1, help="iterations between two halo exchanges")
     ap.add_argument("--check", action="store_true")
     a = ap.parse_args()
     dist.init_process_group("gloo")
     rank, world = dist.get_rank(), dist.get_world_size()
     ch = 3 if a.color == "rgb" else 1
     img = waterfall_image(a.height, a.width, ch, seed=0)
-    eng = GlooHaloBlur(a.width, a.height, ch, threads=a.threads)
+    eng = GlooHaloBlur(a.width, a.height, ch, threads=a.threads, halo_depth=a.halo_depth)
     blk = torch.from_numpy(np.ascontiguousarray(img[eng.r0:eng.r0 + eng.R, eng.c0:eng.c0 + eng.C]))
     eng.load(blk)
     eng.run(2)                       # warm-up
@@ -57,7 +58,7 @@ def main():
             ok = bool((full == b200conv.reference_oracle(img, a.reps, "zero")).all())
     if rank == 0:
         s = float(sec.item())
-        print(json.dumps({"impl": "b200conv cpu arm (gloo ranks x threads)", "ranks": world, "threads_per_rank": a.threads,
+        print(json.dumps({"impl": "b200conv cpu arm (gloo ranks x threads)", "ranks": world, "threads_per_rank": a.threads, "halo_depth": eng.F, "exchanges": eng.exchanges,
                           "grid": list(eng.grid), "width": a.width, "height": a.height, "color": a.color,
                           "repetitions": a.reps, "loop_seconds": s,
                           "gpix_it_per_s": a.width * a.height * a.reps / s / 1e9, "equals_oracle": ok,
