@@ -45,8 +45,8 @@ enum {
     B2C_KERNEL_STREAM = 2, /* register-pipelined temporal blocking, LDG feed   */
     B2C_KERNEL_TMA = 3,    /* same pipeline fed by TMA bulk-tensor tiles       */
     B2C_KERNEL_RESIDENT = 4 /* small images: whole image held in registers for the run
-                              (one GPU, gaussian, zero/torus, row bytes % 8 == 0;
-                              opt-in, never chosen by AUTO) */
+                              (one GPU, gaussian, zero/torus, row bytes % 8 == 0, no check_every);
+                              AUTO picks it whenever the image fits */
 };
 
 /* Error codes (negative returns). */
